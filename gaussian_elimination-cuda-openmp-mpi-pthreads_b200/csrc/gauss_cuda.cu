@@ -1,0 +1,691 @@
+// libgauss_cuda.so -- the C ABI (include/gauss_cuda.h) and the host-side schedule of the blocked
+// no-pivot LU.  The arithmetic lives in lu_simt.cu (FFMA kernels) and tc_gemm.cu (tcgen05 tile engine).
+//
+// Algorithm (two-level right-looking Crout LU on the augmented matrix [A | b], FP32):
+//   outer block K = rows/cols [k0, k0+kb), kb <= NB (NB a multiple of 128), owner rank = K mod world
+//   P1 (owner)  for each 128-wide inner block j of the row panel:
+//                 diag factor -> U-row solve over all columns to the right (RHS column included)
+//                 -> L-col solve + rank-128 update of the panel rows below
+//   bcast       packed row panel [kb x (ld-k0)] to every rank (world > 1)         [gauss_mpi :137]
+//   P2 (all)    for each inner block j: L-col solve of the local rows below the panel,
+//                 rank-128 update of their columns inside [k0, k0+kb)
+//   P3 (all)    local rows below, columns right of the panel:  A22 -= L21 * U12   (K = kb)
+// which reproduces computeGauss (gauss_internal_input.c:118-138) up to rounding order; back
+// substitution (solveGauss :144-159) runs block-wise from the last outer block up.
+#include "gauss_cuda.h"
+#include "gauss_internal.cuh"
+
+#include <dlfcn.h>
+#include <nccl.h>       // types only; the library is loaded lazily with dlopen (single-GPU users never need it)
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <algorithm>
+#include <vector>
+
+using namespace gb200;
+
+// ------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int cuda_fail(cudaError_t e, const char* what, int line)
+{
+    snprintf(g_err, sizeof g_err, "%s (gauss_cuda.cu:%d): %s", what, line, cudaGetErrorString(e));
+    return GAUSS_CUDA_CUDA_ERR;
+}
+#define CK(call)                                                            \
+    do {                                                                    \
+        cudaError_t e_ = (call);                                            \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call, __LINE__);       \
+    } while (0)
+
+extern "C" const char* gauss_cuda_last_error(void) { return g_err; }
+
+extern "C" const char* gauss_cuda_strerror(int st)
+{
+    switch (st) {
+        case GAUSS_CUDA_OK:         return "ok";
+        case GAUSS_CUDA_ZERO_PIVOT: return "The matrix is singular";   // the reference's message, gauss_internal_input.c:87
+        case GAUSS_CUDA_BAD_ARG:    return "bad argument";
+        case GAUSS_CUDA_CUDA_ERR:   return "CUDA error";
+        case GAUSS_CUDA_NCCL_ERR:   return "NCCL error";
+        case GAUSS_CUDA_NOT_READY:  return "no system resident on the device (call gauss_cuda_upload first)";
+        default:                    return "unknown status";
+    }
+}
+
+extern "C" int gauss_cuda_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// ------------------------------------------------------------------------------------------
+// NCCL, loaded on demand
+// ------------------------------------------------------------------------------------------
+struct NcclApi {
+    void* handle = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+static NcclApi g_nccl;
+
+static int nccl_load()
+{
+    if (g_nccl.handle) return GAUSS_CUDA_OK;
+    const char* names[] = {"libnccl.so.2", "/usr/lib/x86_64-linux-gnu/libnccl.so.2", "libnccl.so"};
+    void* h = nullptr;
+    for (const char* nm : names) { h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL); if (h) break; }
+    if (!h) { snprintf(g_err, sizeof g_err, "cannot load libnccl.so.2: %s", dlerror()); return GAUSS_CUDA_NCCL_ERR; }
+    g_nccl.GetUniqueId    = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+    g_nccl.CommInitRank   = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
+    g_nccl.Broadcast      = (decltype(g_nccl.Broadcast))dlsym(h, "ncclBroadcast");
+    g_nccl.CommDestroy    = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.Broadcast || !g_nccl.CommDestroy) {
+        snprintf(g_err, sizeof g_err, "libnccl.so.2 lacks a required symbol");
+        return GAUSS_CUDA_NCCL_ERR;
+    }
+    g_nccl.handle = h;
+    return GAUSS_CUDA_OK;
+}
+static int nccl_fail(ncclResult_t r, const char* what, int line)
+{
+    snprintf(g_err, sizeof g_err, "%s (gauss_cuda.cu:%d): %s", what, line,
+             g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "nccl failure");
+    return GAUSS_CUDA_NCCL_ERR;
+}
+#define NK(call)                                                            \
+    do {                                                                    \
+        ncclResult_t r_ = (call);                                           \
+        if (r_ != ncclSuccess) return nccl_fail(r_, #call, __LINE__);       \
+    } while (0)
+
+extern "C" int gauss_cuda_unique_id(void* id128)
+{
+    if (!id128) return GAUSS_CUDA_BAD_ARG;
+    int rc = nccl_load();
+    if (rc) return rc;
+    ncclUniqueId id;
+    NK(g_nccl.GetUniqueId(&id));
+    memcpy(id128, &id, sizeof id);
+    return GAUSS_CUDA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------
+struct gauss_cuda_ctx {
+    int n = 0, np = 0, ld = 0, NB = 0, mode = 0;
+    int rank = 0, world = 1, device = 0;
+    int nblk = 0;            // outer blocks
+    int rows_local = 0;      // rows of W held by this rank (multiple of 128)
+    float* W = nullptr;      // working augmented matrix  [rows_local x ld]
+    float* W0 = nullptr;     // resident pristine copy (gauss_cuda_upload), same shape
+    float* pbuf = nullptr;   // packed row panel [NB x ld]                      (world > 1)
+    float* la_hi = nullptr, *la_lo = nullptr;   // [rows_local x NB]  split L operand (3xTF32 mode)
+    float* ub_hi = nullptr, *ub_lo = nullptr;   // [ld x NB]          split U operand, transposed
+    float* xvec = nullptr;   // [np] solution
+    float* hvec = nullptr;   // [np] staging for RHS upload / B_out
+    int* status = nullptr;   // device: 0 or (row+1) of the first bad pivot
+    cudaStream_t s_main = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    ncclComm_t comm = nullptr;
+    bool resident = false, factored = false;
+    double bcast_bytes = 0.0;
+    gauss_cuda_stats last{};
+};
+
+static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// rows of outer block R: [R*NB, min((R+1)*NB, np))
+static inline int blk_rows(const gauss_cuda_ctx* c, int R) { return std::min(c->NB, c->np - R * c->NB); }
+// local row offset of outer block R on its owner
+static inline int blk_local_row(const gauss_cuda_ctx* c, int R) { return (R / c->world) * c->NB; }
+// first local block index whose global block index is > K  (rows strictly below outer block K)
+static inline int first_local_block_after(const gauss_cuda_ctx* c, int K) { return K >= c->rank ? (K - c->rank) / c->world + 1 : 0; }
+// number of local blocks whose global block index is < K   (rows strictly above outer block K)
+static inline int local_blocks_before(const gauss_cuda_ctx* c, int K) { return K > c->rank ? (K - c->rank - 1) / c->world + 1 : 0; }
+
+
+static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int device, const void* nccl_id, int nb, int mode)
+{
+    if (!out) return GAUSS_CUDA_BAD_ARG;
+    *out = nullptr;
+    if (n < 1 || world < 1 || rank < 0 || rank >= world) return GAUSS_CUDA_BAD_ARG;
+    if (mode != GAUSS_CUDA_MODE_3XTF32 && mode != GAUSS_CUDA_MODE_FFMA) return GAUSS_CUDA_BAD_ARG;
+    if (nb < 0 || (nb % kNb) != 0) return GAUSS_CUDA_BAD_ARG;
+    if (gauss_cuda_device_count() <= device) {
+        snprintf(g_err, sizeof g_err, "no CUDA device %d (this library has no CPU fallback)", device);
+        return GAUSS_CUDA_CUDA_ERR;
+    }
+    CK(cudaSetDevice(device));
+    if (mode == GAUSS_CUDA_MODE_3XTF32 && !tc_available()) {
+        snprintf(g_err, sizeof g_err, "GAUSS_CUDA_MODE_3XTF32 needs an sm_100 device (tcgen05/TMA)");
+        return GAUSS_CUDA_CUDA_ERR;
+    }
+    gauss_cuda_ctx* c = new gauss_cuda_ctx();
+    c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode;
+    c->np = round_up(n, kNb);
+    c->ld = c->np + kPadCols;
+    if (nb == 0) {
+        if (mode == GAUSS_CUDA_MODE_FFMA) nb = (world > 1) ? 256 : 128;
+        else nb = c->np >= 8192 ? 512 : (c->np >= 2048 ? 256 : 128);
+    }
+    c->NB = std::min(nb, c->np);
+    c->nblk = (c->np + c->NB - 1) / c->NB;
+    int rows = 0;
+    for (int R = rank; R < c->nblk; R += world) rows += blk_rows(c, R);
+    c->rows_local = rows;
+    simt_setup_device();
+    if (mode == GAUSS_CUDA_MODE_3XTF32) { int rc = tc_setup_device(); if (rc) { delete c; return rc; } }
+
+    const size_t wbytes = (size_t)std::max(rows, 1) * c->ld * sizeof(float);
+    cudaError_t e = cudaSuccess;
+    auto A = [&](void** p, size_t bytes) { if (e == cudaSuccess) e = cudaMalloc(p, bytes); };
+    A((void**)&c->W, wbytes);
+    A((void**)&c->xvec, (size_t)c->np * sizeof(float));
+    A((void**)&c->hvec, (size_t)c->np * sizeof(float));
+    A((void**)&c->status, sizeof(int));
+    if (world > 1) A((void**)&c->pbuf, (size_t)c->NB * c->ld * sizeof(float));
+    if (mode == GAUSS_CUDA_MODE_3XTF32) {
+        const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
+        const size_t ub = (size_t)c->ld * c->NB * sizeof(float);
+        A((void**)&c->la_hi, la); A((void**)&c->la_lo, la);
+        A((void**)&c->ub_hi, ub); A((void**)&c->ub_lo, ub);
+        if (e == cudaSuccess) e = cudaMemset(c->ub_hi, 0, ub);
+        if (e == cudaSuccess) e = cudaMemset(c->ub_lo, 0, ub);
+    }
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
+    for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    if (e != cudaSuccess) { int rc = cuda_fail(e, "context allocation", __LINE__); gauss_cuda_free(c); return rc; }
+
+    if (world > 1) {
+        int rc = nccl_load();
+        if (rc) { gauss_cuda_free(c); return rc; }
+        ncclUniqueId id;
+        memcpy(&id, nccl_id, sizeof id);
+        ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
+        if (r != ncclSuccess) { rc = nccl_fail(r, "ncclCommInitRank", __LINE__); gauss_cuda_free(c); return rc; }
+    }
+    *out = c;
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int gauss_cuda_init(gauss_cuda_ctx** ctx, int n, int ngpus, int nb, int mode)
+{
+    if (ngpus != 1) {
+        snprintf(g_err, sizeof g_err, "gauss_cuda_init drives one GPU per process; use gauss_cuda_init_dist for %d", ngpus);
+        return GAUSS_CUDA_BAD_ARG;
+    }
+    int dev = 0;
+    if (gauss_cuda_device_count() > 0) cudaGetDevice(&dev);
+    return ctx_create(ctx, n, 0, 1, dev, nullptr, nb, mode);
+}
+
+extern "C" int gauss_cuda_init_dist(gauss_cuda_ctx** ctx, int n, int rank, int world, int device,
+                                    const void* nccl_id_128, int nb, int mode)
+{
+    if (world > 1 && !nccl_id_128) return GAUSS_CUDA_BAD_ARG;
+    return ctx_create(ctx, n, rank, world, device, nccl_id_128, nb, mode);
+}
+
+extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
+{
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->s_main) cudaStreamSynchronize(c->s_main);
+    if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+    float* bufs[] = {c->W, c->W0, c->pbuf, c->la_hi, c->la_lo, c->ub_hi, c->ub_lo, c->xvec, c->hvec};
+    for (float* b : bufs) if (b) cudaFree(b);
+    if (c->status) cudaFree(c->status);
+    for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->s_main) cudaStreamDestroy(c->s_main);
+    delete c;
+}
+
+// ------------------------------------------------------------------------------------------
+// host <-> device
+// ------------------------------------------------------------------------------------------
+// Copies this rank's rows of [A | b] into `dst` (same shape as W) and writes the identity padding.
+static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const float* B)
+{
+    cudaStream_t s = c->s_main;
+    const int n = c->n;
+    CK(cudaMemcpyAsync(c->hvec, B, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, s));
+    for (int R = c->rank; R < c->nblk; R += c->world) {
+        const int g0 = R * c->NB, l0 = blk_local_row(c, R), rows = blk_rows(c, R);
+        const int real = std::max(0, std::min(rows, n - g0));
+        if (real > 0) {
+            CK(cudaMemcpy2DAsync(dst + (size_t)l0 * c->ld, (size_t)c->ld * sizeof(float),
+                                 A + (size_t)g0 * n, (size_t)n * sizeof(float),
+                                 (size_t)n * sizeof(float), real, cudaMemcpyHostToDevice, s));
+            launch_set_column(dst + (size_t)l0 * c->ld, c->ld, c->np, c->hvec + g0, real, s);
+            // columns [n, ld) of real rows except the RHS column
+            launch_pad_identity(dst, c->ld, l0, g0, real, n, c->ld, s);
+        }
+        if (rows > real) launch_pad_identity(dst, c->ld, l0 + real, g0 + real, rows - real, n, c->ld, s);
+    }
+    CK(cudaGetLastError());
+    return GAUSS_CUDA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// elimination
+// ------------------------------------------------------------------------------------------
+static int gemm_update(gauss_cuda_ctx* c, const float* A, int lda, const float* B, int ldb,
+                       const float* Ahi, const float* Alo, const float* Bhi, const float* Blo,
+                       float* C, int m, int ncols, int k)
+{
+    if (m <= 0 || ncols <= 0) return GAUSS_CUDA_OK;
+    if (c->mode == GAUSS_CUDA_MODE_FFMA) {
+        launch_sgemm_nn(A, lda, B, ldb, C, c->ld, m, ncols, k, -1.f, 1.f, c->s_main);
+        return GAUSS_CUDA_OK;
+    }
+    int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, c->s_main);
+    if (rc) return cuda_fail((cudaError_t)rc, "tc_gemm_nt", __LINE__);
+    return GAUSS_CUDA_OK;
+}
+
+static int factor(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main;
+    const int ld = c->ld, NB = c->NB, np = c->np;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    CK(cudaMemsetAsync(c->status, 0, sizeof(int), s));
+    c->bcast_bytes = 0.0;
+    for (int K = 0; K < c->nblk; ++K) {
+        const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
+        const int ninner = kb / kNb;
+        const bool mine = owner == c->rank;
+        float* P = mine ? c->W + (size_t)blk_local_row(c, K) * ld : nullptr;     // the row panel, in place
+        const int lrow = mine ? blk_local_row(c, K) : 0;
+        // ---- P1: factor the row panel on its owner
+        if (mine) {
+            for (int j = 0; j < ninner; ++j) {
+                const int kk = k0 + j * kNb, r = j * kNb;
+                launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
+                launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+                            tc ? c->ub_hi + (size_t)(kk + kNb) * NB : nullptr, tc ? c->ub_lo + (size_t)(kk + kNb) * NB : nullptr,
+                            NB, r, s);
+                const int mrem = kb - (r + kNb);
+                if (mrem > 0) {
+                    launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
+                                tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB : nullptr,
+                                NB, r, s);
+                    int rc = gemm_update(c, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                                         tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
+                                         tc ? c->ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? c->ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
+                                         P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
+                    if (rc) return rc;
+                }
+            }
+        }
+        // ---- broadcast the factored row panel (the reference's MPI_Bcast of the pivot row, gauss_mpi :137)
+        const float* Pn = P + (mine ? k0 : 0);    // panel origin = element (row k0, col k0)
+        int ldp = ld;
+        if (c->world > 1) {
+            ldp = ld - k0;
+            if (mine)
+                CK(cudaMemcpy2DAsync(c->pbuf, (size_t)ldp * sizeof(float), P + k0, (size_t)ld * sizeof(float),
+                                     (size_t)ldp * sizeof(float), kb, cudaMemcpyDeviceToDevice, s));
+            NK(g_nccl.Broadcast(c->pbuf, c->pbuf, (size_t)kb * ldp, ncclFloat, owner, c->comm, s));
+            if (!mine) c->bcast_bytes += (double)kb * ldp * sizeof(float);
+            Pn = c->pbuf;
+            if (tc && !mine) {
+                // rebuild the split, transposed U operand from the raw panel: columns right of each inner block
+                for (int j = 0; j < ninner; ++j) {
+                    const int r = j * kNb, cfirst = r + kNb;          // panel-relative first column
+                    launch_split_transpose(Pn + (size_t)r * ldp + cfirst, ldp,
+                                           c->ub_hi + (size_t)(k0 + cfirst) * NB + r, c->ub_lo + (size_t)(k0 + cfirst) * NB + r,
+                                           NB, kNb, ldp - cfirst, kNb, s);
+                }
+            }
+        }
+        // ---- P2 + P3 on the local rows below the panel
+        const int l0 = first_local_block_after(c, K) * NB;
+        const int mbelow = c->rows_local - l0;
+        if (mbelow > 0) {
+            float* Wb = c->W + (size_t)l0 * ld;
+            for (int j = 0; j < ninner; ++j) {
+                const int kk = k0 + j * kNb, r = j * kNb;
+                launch_lcol(Pn + (size_t)r * ldp + r, ldp, Wb + kk, ld, mbelow,
+                            tc ? c->la_hi + (size_t)l0 * NB : nullptr, tc ? c->la_lo + (size_t)l0 * NB : nullptr, NB, r, s);
+                const int nin = kb - (r + kNb);           // columns of the panel still to the right
+                if (nin > 0) {
+                    int rc = gemm_update(c, Wb + kk, ld, Pn + (size_t)r * ldp + r + kNb, ldp,
+                                         tc ? c->la_hi + (size_t)l0 * NB + r : nullptr, tc ? c->la_lo + (size_t)l0 * NB + r : nullptr,
+                                         tc ? c->ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? c->ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
+                                         Wb + kk + kNb, mbelow, nin, kNb);
+                    if (rc) return rc;
+                }
+            }
+            int rc = gemm_update(c, Wb + k0, ld, Pn + kb, ldp,
+                                 c->la_hi ? c->la_hi + (size_t)l0 * NB : nullptr, c->la_lo ? c->la_lo + (size_t)l0 * NB : nullptr,
+                                 c->ub_hi ? c->ub_hi + (size_t)(k0 + kb) * NB : nullptr, c->ub_lo ? c->ub_lo + (size_t)(k0 + kb) * NB : nullptr,
+                                 Wb + k0 + kb, mbelow, ld - (k0 + kb), kb);
+            if (rc) return rc;
+        }
+    }
+    CK(cudaGetLastError());
+    c->factored = true;
+    return GAUSS_CUDA_OK;
+}
+
+// Back substitution, solveGauss (gauss_internal_input.c:144-159): outer blocks from the last up;
+// the owner solves its diagonal blocks, x_K travels to everyone, every rank folds it into its y.
+static int backsub(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main;
+    const int ld = c->ld, NB = c->NB, np = c->np;
+    for (int K = c->nblk - 1; K >= 0; --K) {
+        const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
+        const int ninner = kb / kNb;
+        if (owner == c->rank) {
+            float* P = c->W + (size_t)blk_local_row(c, K) * ld;
+            for (int j = ninner - 1; j >= 0; --j) {
+                const int kk = k0 + j * kNb, r = j * kNb;
+                launch_trsv_diag(P + (size_t)r * ld + kk, ld, np - kk, c->xvec + kk, s);
+                launch_trsv_gemv(P + kk, ld, np - kk, c->xvec + kk, r, s);      // panel rows above this inner block
+            }
+        }
+        if (c->world > 1) {
+            NK(g_nccl.Broadcast(c->xvec + k0, c->xvec + k0, (size_t)kb, ncclFloat, owner, c->comm, s));
+            if (owner != c->rank) c->bcast_bytes += (double)kb * sizeof(float);
+        }
+        const int mabove = local_blocks_before(c, K) * NB;
+        for (int j = 0; j < ninner && mabove > 0; ++j) {
+            const int kk = k0 + j * kNb;
+            launch_trsv_gemv(c->W + kk, ld, np - kk, c->xvec + kk, mabove, s);
+        }
+    }
+    CK(cudaGetLastError());
+    return GAUSS_CUDA_OK;
+}
+
+static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool fac, bool bs, bool d2h)
+{
+    CK(cudaStreamSynchronize(c->s_main));
+    int flag = 0;
+    CK(cudaMemcpy(&flag, c->status, sizeof(int), cudaMemcpyDeviceToHost));
+    gauss_cuda_stats& o = c->last;
+    auto el = [&](int a, int b) { float ms = 0.f; cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]); return (double)ms * 1e-3; };
+    o.h2d_s = h2d ? el(0, 1) : 0.0;
+    o.factor_s = fac ? el(1, 2) : 0.0;
+    o.backsub_s = bs ? el(2, 3) : 0.0;
+    o.d2h_s = d2h ? el(3, 4) : 0.0;
+    o.bcast_bytes = c->bcast_bytes;
+    o.zero_pivot_row = flag ? flag - 1 : -1;
+    o.n = c->n; o.n_padded = c->np; o.nb_outer = c->NB; o.nb_inner = kNb; o.mode = c->mode; o.rank = c->rank; o.world = c->world;
+    o.kernel_launches = g_launch_count;
+    if (st) *st = o;
+    return flag ? GAUSS_CUDA_ZERO_PIVOT : GAUSS_CUDA_OK;
+}
+
+// X is complete on every rank after back substitution; B after elimination is spread over the ranks.
+static int download_results(gauss_cuda_ctx* c, float* X, float* B_out)
+{
+    cudaStream_t s = c->s_main;
+    if (X) CK(cudaMemcpyAsync(X, c->xvec, (size_t)c->n * sizeof(float), cudaMemcpyDeviceToHost, s));
+    if (B_out) {
+        // hvec holds this rank's rows of y = L^-1 b (snapshot_rhs); the other ranks' rows arrive here,
+        // one small broadcast per outer block (collective: every rank must ask for B_out or none).
+        if (c->world > 1)
+            for (int R = 0; R < c->nblk; ++R)
+                NK(g_nccl.Broadcast(c->hvec + R * c->NB, c->hvec + R * c->NB, (size_t)blk_rows(c, R), ncclFloat, R % c->world, c->comm, s));
+        CK(cudaMemcpyAsync(B_out, c->hvec, (size_t)c->n * sizeof(float), cudaMemcpyDeviceToHost, s));
+    }
+    return GAUSS_CUDA_OK;
+}
+
+// After elimination, snapshot this rank's rows of the RHS column (y = L^-1 b) into hvec so that B_out
+// survives back substitution, which overwrites that column with x.
+static int snapshot_rhs(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main;
+    for (int R = c->rank; R < c->nblk; R += c->world) {
+        const int g0 = R * c->NB, l0 = blk_local_row(c, R), rows = blk_rows(c, R);
+        launch_get_column(c->W + (size_t)l0 * c->ld, c->ld, c->np, c->hvec + g0, rows, s);
+    }
+    CK(cudaGetLastError());
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* B, float* X, float* B_out, gauss_cuda_stats* st)
+{
+    if (!c || !A || !B || !X) return GAUSS_CUDA_BAD_ARG;
+    CK(cudaSetDevice(c->device));
+    g_launch_count = 0;
+    cudaStream_t s = c->s_main;
+    int rc;
+    CK(cudaEventRecord(c->ev[0], s));
+    if ((rc = upload_into(c, c->W, A, B))) return rc;
+    CK(cudaEventRecord(c->ev[1], s));
+    if ((rc = factor(c))) return rc;
+    CK(cudaEventRecord(c->ev[2], s));
+    if (B_out && (rc = snapshot_rhs(c))) return rc;
+    if ((rc = backsub(c))) return rc;
+    CK(cudaEventRecord(c->ev[3], s));
+    if ((rc = download_results(c, X, B_out))) return rc;
+    CK(cudaEventRecord(c->ev[4], s));
+    return finish_stats(c, st, true, true, true, true);
+}
+
+extern "C" int gauss_cuda_upload(gauss_cuda_ctx* c, const float* A, const float* B)
+{
+    if (!c || !A || !B) return GAUSS_CUDA_BAD_ARG;
+    CK(cudaSetDevice(c->device));
+    if (!c->W0) CK(cudaMalloc((void**)&c->W0, (size_t)std::max(c->rows_local, 1) * c->ld * sizeof(float)));
+    int rc = upload_into(c, c->W0, A, B);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(c->s_main));
+    c->resident = true;
+    c->factored = false;
+    return GAUSS_CUDA_OK;
+}
+
+static int restore_working(gauss_cuda_ctx* c)
+{
+    CK(cudaMemcpyAsync(c->W, c->W0, (size_t)c->rows_local * c->ld * sizeof(float), cudaMemcpyDeviceToDevice, c->s_main));
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int gauss_cuda_solve_resident(gauss_cuda_ctx* c, gauss_cuda_stats* st)
+{
+    if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->resident) return GAUSS_CUDA_NOT_READY;
+    CK(cudaSetDevice(c->device));
+    g_launch_count = 0;
+    cudaStream_t s = c->s_main;
+    int rc;
+    CK(cudaEventRecord(c->ev[0], s));
+    if ((rc = restore_working(c))) return rc;
+    CK(cudaEventRecord(c->ev[1], s));
+    if ((rc = factor(c))) return rc;
+    CK(cudaEventRecord(c->ev[2], s));
+    if ((rc = snapshot_rhs(c))) return rc;
+    if ((rc = backsub(c))) return rc;
+    CK(cudaEventRecord(c->ev[3], s));
+    CK(cudaEventRecord(c->ev[4], s));
+    return finish_stats(c, st, true, true, true, false);
+}
+
+extern "C" int gauss_cuda_compute_gauss(gauss_cuda_ctx* c, gauss_cuda_stats* st)
+{
+    if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->resident) return GAUSS_CUDA_NOT_READY;
+    CK(cudaSetDevice(c->device));
+    g_launch_count = 0;
+    cudaStream_t s = c->s_main;
+    int rc;
+    CK(cudaEventRecord(c->ev[0], s));
+    if ((rc = restore_working(c))) return rc;
+    CK(cudaEventRecord(c->ev[1], s));
+    if ((rc = factor(c))) return rc;
+    CK(cudaEventRecord(c->ev[2], s));
+    if ((rc = snapshot_rhs(c))) return rc;
+    CK(cudaEventRecord(c->ev[3], s));
+    CK(cudaEventRecord(c->ev[4], s));
+    return finish_stats(c, st, true, true, false, false);
+}
+
+extern "C" int gauss_cuda_solve_gauss(gauss_cuda_ctx* c, gauss_cuda_stats* st)
+{
+    if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->resident || !c->factored) return GAUSS_CUDA_NOT_READY;
+    CK(cudaSetDevice(c->device));
+    g_launch_count = 0;
+    cudaStream_t s = c->s_main;
+    int rc;
+    CK(cudaEventRecord(c->ev[2], s));
+    if ((rc = backsub(c))) return rc;
+    CK(cudaEventRecord(c->ev[3], s));
+    c->factored = false;                     // the RHS column now holds x: a second call would be wrong
+    return finish_stats(c, st, false, false, true, false);
+}
+
+extern "C" int gauss_cuda_download(gauss_cuda_ctx* c, float* X, float* B_out)
+{
+    if (!c) return GAUSS_CUDA_BAD_ARG;
+    CK(cudaSetDevice(c->device));
+    int rc = download_results(c, X, B_out);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize(c->s_main));
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int gauss_cuda_download_factors(gauss_cuda_ctx* c, float* LU)
+{
+    if (!c || !LU) return GAUSS_CUDA_BAD_ARG;
+    if (c->world != 1) return GAUSS_CUDA_BAD_ARG;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpy2DAsync(LU, (size_t)c->n * sizeof(float), c->W, (size_t)c->ld * sizeof(float),
+                         (size_t)c->n * sizeof(float), c->n, cudaMemcpyDeviceToHost, c->s_main));
+    CK(cudaStreamSynchronize(c->s_main));
+    return GAUSS_CUDA_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// FP32 matrix multiply
+// ------------------------------------------------------------------------------------------
+struct MatmulScratch {            // per device, grown on demand, kept until process exit
+    float* buf = nullptr;
+    size_t bytes = 0;
+};
+static MatmulScratch g_mm[16];
+
+static int mm_scratch(int dev, size_t bytes, float** out)
+{
+    MatmulScratch& sc = g_mm[dev & 15];
+    if (sc.bytes < bytes) {
+        if (sc.buf) { CK(cudaDeviceSynchronize()); CK(cudaFree(sc.buf)); sc.buf = nullptr; sc.bytes = 0; }
+        CK(cudaMalloc((void**)&sc.buf, bytes));
+        sc.bytes = bytes;
+    }
+    *out = sc.buf;
+    return GAUSS_CUDA_OK;
+}
+
+// Core of both entry points: C = A*B on device pointers with caller-provided scratch (3xTF32 mode:
+// 4 * n * kp floats, kp = n rounded up to 32; FFMA mode with n % 16 != 0: 3 padded copies).
+size_t matmul_scratch_bytes(int n, int mode)
+{
+    if (mode == GAUSS_CUDA_MODE_3XTF32) {
+        const size_t kp = (size_t)round_up(n, 32);
+        size_t b = 4 * (size_t)n * kp * sizeof(float);
+        if (n % 4) b += (size_t)n * round_up(n, 4) * sizeof(float);     // padded C
+        return b;
+    }
+    if (n % 16 == 0) return 0;
+    const size_t p = (size_t)round_up(n, 16);
+    return 3 * p * p * sizeof(float);
+}
+
+int matmul_on_device(const float* dA, const float* dB, float* dC, int n, int mode, float* scratch, cudaStream_t s)
+{
+    if (mode == GAUSS_CUDA_MODE_FFMA) {
+        if (n % 16 == 0) {
+            launch_sgemm_nn(dA, n, dB, n, dC, n, n, n, n, 1.f, 0.f, s);
+        } else {
+            const int p = round_up(n, 16);
+            float* pa = scratch, *pb = scratch + (size_t)p * p, *pc = pb + (size_t)p * p;
+            CK(cudaMemsetAsync(pa, 0, 2 * (size_t)p * p * sizeof(float), s));
+            CK(cudaMemcpy2DAsync(pa, (size_t)p * 4, dA, (size_t)n * 4, (size_t)n * 4, n, cudaMemcpyDeviceToDevice, s));
+            CK(cudaMemcpy2DAsync(pb, (size_t)p * 4, dB, (size_t)n * 4, (size_t)n * 4, n, cudaMemcpyDeviceToDevice, s));
+            launch_sgemm_nn(pa, p, pb, p, pc, p, n, p, p, 1.f, 0.f, s);
+            CK(cudaMemcpy2DAsync(dC, (size_t)n * 4, pc, (size_t)p * 4, (size_t)n * 4, n, cudaMemcpyDeviceToDevice, s));
+        }
+        CK(cudaGetLastError());
+        return GAUSS_CUDA_OK;
+    }
+    const int kp = round_up(n, 32);
+    float* ahi = scratch, *alo = ahi + (size_t)n * kp, *bhi = alo + (size_t)n * kp, *blo = bhi + (size_t)n * kp;
+    launch_split_rowmajor(dA, n, ahi, alo, kp, n, n, s);
+    launch_split_transpose(dB, n, bhi, blo, kp, n, n, kp, s);
+    float* cdst = dC;
+    int ldc = n;
+    if (n % 4) { cdst = blo + (size_t)n * kp; ldc = round_up(n, 4); }
+    int rc = tc_gemm_nt(ahi, alo, kp, bhi, blo, kp, cdst, ldc, n, n, kp, +1, 0, s);
+    if (rc) return cuda_fail((cudaError_t)rc, "tc_gemm_nt", __LINE__);
+    if (cdst != dC) CK(cudaMemcpy2DAsync(dC, (size_t)n * 4, cdst, (size_t)ldc * 4, (size_t)n * 4, n, cudaMemcpyDeviceToDevice, s));
+    CK(cudaGetLastError());
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int matmul_cuda_device(const float* dA, const float* dB, float* dC, int n, int mode, void* stream)
+{
+    if (!dA || !dB || !dC || n < 1) return GAUSS_CUDA_BAD_ARG;
+    if (mode != GAUSS_CUDA_MODE_3XTF32 && mode != GAUSS_CUDA_MODE_FFMA) return GAUSS_CUDA_BAD_ARG;
+    if (gauss_cuda_device_count() < 1) { snprintf(g_err, sizeof g_err, "no CUDA device (no CPU fallback)"); return GAUSS_CUDA_CUDA_ERR; }
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    simt_setup_device();
+    if (mode == GAUSS_CUDA_MODE_3XTF32) {
+        if (!tc_available()) { snprintf(g_err, sizeof g_err, "GAUSS_CUDA_MODE_3XTF32 needs an sm_100 device"); return GAUSS_CUDA_CUDA_ERR; }
+        int rc = tc_setup_device();
+        if (rc) return rc;
+    }
+    float* scratch = nullptr;
+    const size_t need = matmul_scratch_bytes(n, mode);
+    if (need) { int rc = mm_scratch(dev, need, &scratch); if (rc) return rc; }
+    return matmul_on_device(dA, dB, dC, n, mode, scratch, (cudaStream_t)stream);
+}
+
+extern "C" int matmul_cuda(const float* A, const float* B, float* C, int n, int mode, double* kernel_s)
+{
+    if (!A || !B || !C || n < 1) return GAUSS_CUDA_BAD_ARG;
+    if (gauss_cuda_device_count() < 1) { snprintf(g_err, sizeof g_err, "no CUDA device (no CPU fallback)"); return GAUSS_CUDA_CUDA_ERR; }
+    g_launch_count = 0;
+    const size_t bytes = (size_t)n * n * sizeof(float);
+    float* d = nullptr;
+    CK(cudaMalloc((void**)&d, 3 * bytes));
+    float* dA = d, *dB = d + (size_t)n * n, *dC = dB + (size_t)n * n;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    int rc = GAUSS_CUDA_OK;
+    cudaError_t e = cudaMemcpy(dA, A, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dB, B, bytes, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        cudaEventRecord(e0, 0);
+        rc = matmul_cuda_device(dA, dB, dC, n, mode, nullptr);
+        cudaEventRecord(e1, 0);
+        if (rc == GAUSS_CUDA_OK) e = cudaMemcpy(C, dC, bytes, cudaMemcpyDeviceToHost);
+    }
+    if (rc == GAUSS_CUDA_OK && e == cudaSuccess && kernel_s) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        *kernel_s = (double)ms * 1e-3;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    cudaFree(d);
+    if (rc) return rc;
+    if (e != cudaSuccess) return cuda_fail(e, "matmul_cuda copies", __LINE__);
+    return GAUSS_CUDA_OK;
+}

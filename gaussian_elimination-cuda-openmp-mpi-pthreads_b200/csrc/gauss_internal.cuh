@@ -1,0 +1,67 @@
+// Internal declarations shared by the translation units of libgauss_cuda.so.
+// Nothing here is part of the C ABI (include/gauss_cuda.h is).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gb200 {
+
+constexpr int kNb = 128;          // inner block: diagonal factor / substitution kernels
+constexpr int kPadCols = 32;      // zero columns after the RHS column (keeps rows 128 B aligned)
+
+// ---- SIMT kernels (lu_simt.cu) ---------------------------------------------------------
+
+// In-place Crout factor of the 128x128 block at `blk` (leading dimension ld):
+// U unit-upper above the diagonal, L (pivots included) on and below it.
+// `status` receives (global_row + 1) of the first zero / non-finite pivot (0 = none).
+void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s);
+
+// U-row: X = L11^-1 * A12 for the 128-row block `rows` over `ncols` columns starting at
+// `a12` (ld); L11 is the lower triangle (with pivots) of the 128x128 block at `l11` (ldl).
+// If ub_hi != nullptr also writes the TF32 hi/lo split of X TRANSPOSED:
+// ub_{hi,lo}[(col0_ub + c) * ldub + k_ub + r] for column c, row r (B-role operand, K-major).
+void launch_urow(const float* l11, int ldl, float* a12, int ld, int ncols,
+                 float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s);
+
+// L-col: X = A21 * U11^-1 for `nrows` rows starting at `a21` (ld), 128 columns; U11 is the
+// strict upper triangle (unit diagonal implied) of the block at `u11` (ldu).
+// If la_hi != nullptr also writes the hi/lo split of X: la_{hi,lo}[r * ldla + k_la + c].
+void launch_lcol(const float* u11, int ldu, float* a21, int ld, int nrows,
+                 float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s);
+
+// FP32 FFMA GEMM: C[m x n] = beta*C + alpha*A[m x k]*B[k x n], row-major, alpha in {+1,-1}, beta in {0,1}.
+// m, n arbitrary (n and all leading dimensions multiples of 4, pointers 16 B aligned), k multiple of 16.
+void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                     int m, int n, int k, float alpha, float beta, cudaStream_t s);
+
+// Back substitution pieces (unit-upper U):
+//  trsv_diag:  x[0..128) = U_kk^-1 * y_k for the 128x128 diagonal block at `ukk`; y is read from
+//              column `ycol` of the same rows (ycol relative to ukk), x also written back there.
+//  trsv_gemv:  y[r] -= U[r, blk] . x  for `nrows` rows starting at `u` (ld), y at column offset ycol.
+void launch_trsv_diag(float* ukk, int ld, int ycol, float* x, cudaStream_t s);
+void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cudaStream_t s);
+
+// Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.
+void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s);
+void launch_get_column(const float* w, int ld, int col, float* dst, int nrows, cudaStream_t s);
+void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int width, cudaStream_t s);
+
+// matmul operand preparation for the tensor-core path: A -> hi/lo (row-major), B -> hi/lo transposed.
+void launch_split_rowmajor(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, cudaStream_t s);
+// split_transpose: hi/lo[c*ldd + r] = split(src[r*lds + c]) for c < cols, r < rext (source rows >= rows read as 0).
+void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, int rext, cudaStream_t s);
+void simt_setup_device();     // per-device dynamic shared memory opt-ins of the SIMT kernels
+int  tc_setup_device();       // same for the tile engine; returns a GAUSS_CUDA_* status
+
+// ---- tensor-core tile engine (tc_gemm.cu) -----------------------------------------------
+
+// C[m x n] (ldc) = beta*C - or + (Ahi+Alo)[m x k] * (Bhi+Blo)[n x k]^T as three TF32 MMAs per k-slice.
+// A* are [m x k] K-major (lda), B* are [n x k] K-major (ldb); sign = -1 subtracts, +1 adds; beta in {0,1}.
+// k multiple of 32.  Returns a cudaError_t-compatible code (0 = ok).
+int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
+               float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s);
+bool tc_available();
+
+extern thread_local long long g_launch_count;   // kernels launched by this thread since last reset
+
+} // namespace gb200

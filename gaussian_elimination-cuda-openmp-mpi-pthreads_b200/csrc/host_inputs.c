@@ -1,0 +1,50 @@
+/* Host-side input generators shared by libgauss_cuda.so and the C harness (include/gauss_cuda.h).
+ * Plain C, no CUDA. */
+#include "gauss_cuda.h"
+#include <math.h>
+#include <stddef.h>
+#include <stdlib.h>
+
+/* The reference's built-in fixture, gauss_internal_input.c:50-60. */
+void gauss_host_init_matrix(double *A, double *B, int n)
+{
+    for (int i = 0; i < n; ++i) {
+        for (int j = 0; j < n; ++j)
+            A[(size_t)i * n + j] = (j < i) ? 2.0 * (j + 1) : 2.0 * (i + 1);
+        B[i] = (double)i;
+    }
+}
+
+/* Seeded mode: uniform rand()/32768.0 entries made strictly diagonally dominant (a no-pivot FP32
+ * solver cannot meet 1e-3 on un-dominated random matrices), preset solution i+1 and
+ * B = A * X_true in double as the reference's initRHS does (gauss_external_input.c:88-106). */
+void gauss_host_initialize_inputs(double *A, double *B, double *X_true, int n, unsigned seed)
+{
+    srand(seed);
+    for (int i = 0; i < n; ++i) {
+        double rowsum = 0.0;
+        for (int j = 0; j < n; ++j) {
+            const double v = (double)rand() / 32768.0;
+            A[(size_t)i * n + j] = v;
+            rowsum += fabs(v);
+        }
+        A[(size_t)i * n + i] += rowsum;
+    }
+    for (int i = 0; i < n; ++i) X_true[i] = (double)(i + 1);
+    for (int i = 0; i < n; ++i) {
+        double r = 0.0;
+        for (int j = 0; j < n; ++j) r += A[(size_t)i * n + j] * X_true[j];
+        B[i] = r;
+    }
+}
+
+/* cuda_matmul.cu:126-132 */
+void gauss_host_matmul_fill(float *A, float *B, int n)
+{
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j < n; ++j) {
+            const int idx = (int)(float)(j + i * n);
+            A[idx] = idx + 1.0f;
+            B[idx] = 1.0f / (idx + 1.0f);
+        }
+}

@@ -1,0 +1,589 @@
+// SIMT (FP32 FFMA) kernels of the blocked no-pivot LU: the latency-critical diagonal-block
+// factor, the two triangular panel solves, the FFMA GEMM used by GAUSS_CUDA_MODE_FFMA, the
+// blocked back substitution and a few layout helpers.  sm_100a only.
+//
+// Reference semantics being reproduced (OpenMP_and_MPI/gauss_openmp/gauss_internal_input.c):
+//   getPivot  :100-111  row i is divided by its pivot (true division), diagonal becomes 1
+//   computeGauss :129-136  rows j>i:  m = a_ji ; a_j[i+1:] -= m * a_i[i+1:] ; b_j -= m * b_i
+//   solveGauss :144-159  unit-diagonal back substitution
+// i.e. Crout LU: A = L*U, U unit upper, L carries the pivots; the RHS is carried as an extra
+// matrix column so `b_j -= m*b_i` (:135) needs no code of its own.
+#include "gauss_internal.cuh"
+
+namespace gb200 {
+
+thread_local long long g_launch_count = 0;
+
+__device__ __forceinline__ float tf32_hi(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
+    hi = tf32_hi(x);
+    lo = tf32_hi(x - hi);
+}
+
+// =====================================================================================
+// 1. Diagonal block factor: 128x128, one CTA of 256 threads, the block lives in registers
+//    (16x16 thread grid, cyclic 8x8 elements per thread); per pivot step the normalised
+//    pivot row and the multiplier column are exchanged through double-buffered shared
+//    memory (one __syncthreads per step), the pivot itself by a warp shuffle.
+// =====================================================================================
+template <int PH>
+__device__ __forceinline__ void diag_phase(float (&a)[8][8], float (&rowbuf)[2][kNb], float (&colbuf)[2][kNb],
+                                           const int tx, const int ty, const int warp, int& bad)
+{
+#pragma unroll 1
+    for (int kk = 0; kk < 16; ++kk) {
+        const int k = PH * 16 + kk;
+        float* rb = rowbuf[k & 1];
+        float* cb = colbuf[k & 1];
+        if (warp == (kk >> 1)) {                      // the warp holding row k (warp-uniform branch)
+            const float piv = __shfl_sync(0xffffffffu, a[PH][PH], ((kk & 1) << 4) | kk);
+            if (ty == kk) {
+                if (tx == kk && (!(fabsf(piv) > 0.f) || isinf(piv)) && bad < 0) bad = k;
+#pragma unroll
+                for (int q = PH; q < 8; ++q) {
+                    const int j = tx + 16 * q;
+                    if (j > k) {
+                        a[PH][q] = __fdiv_rn(a[PH][q], piv);     // getPivot :105-107
+                        rb[j] = a[PH][q];
+                    }
+                }
+            }
+        }
+        if (tx == kk) {
+#pragma unroll
+            for (int p = PH; p < 8; ++p) {
+                const int i = ty + 16 * p;
+                if (i > k) cb[i] = a[p][PH];
+            }
+        }
+        __syncthreads();
+        float rv[8];
+#pragma unroll
+        for (int q = PH; q < 8; ++q) rv[q] = rb[tx + 16 * q];
+#pragma unroll
+        for (int p = PH; p < 8; ++p) {
+            const int i = ty + 16 * p;
+            if (i > k) {
+                const float l = cb[i];
+#pragma unroll
+                for (int q = PH; q < 8; ++q)
+                    if (tx + 16 * q > k) a[p][q] = fmaf(-l, rv[q], a[p][q]);   // computeGauss :132-134
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256, 1)
+diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__ status)
+{
+    __shared__ float rowbuf[2][kNb];
+    __shared__ float colbuf[2][kNb];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5;
+    float a[8][8];
+#pragma unroll
+    for (int p = 0; p < 8; ++p)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) a[p][q] = blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q];
+    int bad = -1;
+    diag_phase<0>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<1>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<2>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<3>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<4>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<5>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<6>(a, rowbuf, colbuf, tx, ty, warp, bad);
+    diag_phase<7>(a, rowbuf, colbuf, tx, ty, warp, bad);
+#pragma unroll
+    for (int p = 0; p < 8; ++p)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q] = a[p][q];
+    if (bad >= 0) atomicCAS(status, 0, grow0 + bad + 1);
+}
+
+void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s)
+{
+    diag_factor_kernel<<<1, 256, 0, s>>>(blk, ld, global_row0, status);
+    ++g_launch_count;
+}
+
+// =====================================================================================
+// 2. U-row panel: X = L11^-1 * A12.  One thread per matrix column, 64 columns per CTA,
+//    the 128-row strip in shared memory; 32-row sub-blocks: an unrolled in-register
+//    triangular solve, then a rank-32 update of the rows below.
+// =====================================================================================
+constexpr int kStripW = 64;
+struct UrowSmem {
+    float L[kNb][kNb];            // row-major L11 (only i >= j read)
+    float Ld[4][32][32];          // Ld[b][j][i] = L[32b+i][32b+j]  (transposed diagonal sub-blocks)
+    float strip[kNb][kStripW];
+};
+
+__global__ void __launch_bounds__(kStripW)
+urow_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int ld, int ncols,
+            float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    UrowSmem& sm = *reinterpret_cast<UrowSmem*>(smem_raw);
+    const int tx = threadIdx.x;
+    const int c = blockIdx.x * kStripW + tx;
+    const bool live = c < ncols;
+
+    // L11 -> smem, float4, coalesced
+    for (int idx = tx; idx < kNb * kNb / 4; idx += kStripW) {
+        const int r = idx >> 5, c4 = (idx & 31) << 2;
+        const float4 v = *reinterpret_cast<const float4*>(l11 + (size_t)r * ldl + c4);
+        *reinterpret_cast<float4*>(&sm.L[r][c4]) = v;
+    }
+    for (int r = 0; r < kNb; ++r) sm.strip[r][tx] = live ? a12[(size_t)r * ld + c] : 0.f;
+    __syncthreads();
+    for (int idx = tx; idx < 4 * 32 * 32; idx += kStripW) {
+        const int b = idx >> 10, j = (idx >> 5) & 31, i = idx & 31;
+        sm.Ld[b][j][i] = sm.L[32 * b + i][32 * b + j];
+    }
+    __syncthreads();
+
+#pragma unroll 1
+    for (int b = 0; b < 4; ++b) {
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = sm.strip[32 * b + i][tx];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            x[j] = __fdiv_rn(x[j], sm.Ld[b][j][j]);               // getPivot :105-107 (division by the pivot)
+#pragma unroll
+            for (int i = j + 1; i < 32; ++i) x[i] = fmaf(-sm.Ld[b][j][i], x[j], x[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sm.strip[32 * b + i][tx] = x[i];
+        // rows below this sub-block: strip[r] -= L[r][32b .. 32b+31] . x
+#pragma unroll 1
+        for (int r = 32 * (b + 1); r < kNb; r += 4) {
+            float acc0 = sm.strip[r][tx], acc1 = sm.strip[r + 1][tx], acc2 = sm.strip[r + 2][tx], acc3 = sm.strip[r + 3][tx];
+#pragma unroll
+            for (int j4 = 0; j4 < 32; j4 += 4) {
+                const float4 l0 = *reinterpret_cast<const float4*>(&sm.L[r][32 * b + j4]);
+                const float4 l1 = *reinterpret_cast<const float4*>(&sm.L[r + 1][32 * b + j4]);
+                const float4 l2 = *reinterpret_cast<const float4*>(&sm.L[r + 2][32 * b + j4]);
+                const float4 l3 = *reinterpret_cast<const float4*>(&sm.L[r + 3][32 * b + j4]);
+                acc0 = fmaf(-l0.x, x[j4], acc0); acc0 = fmaf(-l0.y, x[j4 + 1], acc0); acc0 = fmaf(-l0.z, x[j4 + 2], acc0); acc0 = fmaf(-l0.w, x[j4 + 3], acc0);
+                acc1 = fmaf(-l1.x, x[j4], acc1); acc1 = fmaf(-l1.y, x[j4 + 1], acc1); acc1 = fmaf(-l1.z, x[j4 + 2], acc1); acc1 = fmaf(-l1.w, x[j4 + 3], acc1);
+                acc2 = fmaf(-l2.x, x[j4], acc2); acc2 = fmaf(-l2.y, x[j4 + 1], acc2); acc2 = fmaf(-l2.z, x[j4 + 2], acc2); acc2 = fmaf(-l2.w, x[j4 + 3], acc2);
+                acc3 = fmaf(-l3.x, x[j4], acc3); acc3 = fmaf(-l3.y, x[j4 + 1], acc3); acc3 = fmaf(-l3.z, x[j4 + 2], acc3); acc3 = fmaf(-l3.w, x[j4 + 3], acc3);
+            }
+            sm.strip[r][tx] = acc0; sm.strip[r + 1][tx] = acc1; sm.strip[r + 2][tx] = acc2; sm.strip[r + 3][tx] = acc3;
+        }
+    }
+    if (!live) return;
+    for (int r = 0; r < kNb; ++r) a12[(size_t)r * ld + c] = sm.strip[r][tx];
+    if (ub_hi != nullptr) {
+        float* dh = ub_hi + (size_t)c * ldub + k_ub;
+        float* dl = ub_lo + (size_t)c * ldub + k_ub;
+        for (int r = 0; r < kNb; r += 4) {
+            float4 h, l;
+            tf32_split(sm.strip[r][tx], h.x, l.x);
+            tf32_split(sm.strip[r + 1][tx], h.y, l.y);
+            tf32_split(sm.strip[r + 2][tx], h.z, l.z);
+            tf32_split(sm.strip[r + 3][tx], h.w, l.w);
+            *reinterpret_cast<float4*>(dh + r) = h;
+            *reinterpret_cast<float4*>(dl + r) = l;
+        }
+    }
+}
+
+void launch_urow(const float* l11, int ldl, float* a12, int ld, int ncols,
+                 float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s)
+{
+    if (ncols <= 0) return;
+    urow_kernel<<<(ncols + kStripW - 1) / kStripW, kStripW, sizeof(UrowSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
+    ++g_launch_count;
+}
+
+// =====================================================================================
+// 3. L-col panel: X = A21 * U11^-1 (U11 unit upper).  One thread per matrix row, 64 rows
+//    per CTA; mirror image of the U-row kernel.
+// =====================================================================================
+constexpr int kTileH = 64;
+constexpr int kUtLd = kNb + 4;
+struct LcolSmem {
+    float Ut[kNb][kUtLd];         // Ut[j][i] = U[i][j]
+    float Ud[4][32][32];          // Ud[b][i][j] = U[32b+i][32b+j]
+    float tile[kTileH][kNb + 1];
+};
+
+__global__ void __launch_bounds__(kTileH)
+lcol_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int ld, int nrows,
+            float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    LcolSmem& sm = *reinterpret_cast<LcolSmem*>(smem_raw);
+    const int tx = threadIdx.x;
+    const int row0 = blockIdx.x * kTileH;
+    const int lane = tx & 31, wrp = tx >> 5;
+
+    // U11 -> Ut (transposed) and Ud; coalesced global reads (a warp reads 32 consecutive j of one row i)
+    for (int i = wrp; i < kNb; i += kTileH / 32) {
+#pragma unroll
+        for (int jj = 0; jj < kNb; jj += 32) {
+            const int j = jj + lane;
+            const float v = u11[(size_t)i * ldu + j];
+            sm.Ut[j][i] = v;
+            if ((i >> 5) == (j >> 5)) sm.Ud[i >> 5][i & 31][j & 31] = v;
+        }
+    }
+    // tile rows -> smem (a warp reads one row's 128 floats as float4)
+    for (int r = wrp; r < kTileH; r += kTileH / 32) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row0 + r < nrows) v = *reinterpret_cast<const float4*>(a21 + (size_t)(row0 + r) * ld + 4 * lane);
+        sm.tile[r][4 * lane] = v.x; sm.tile[r][4 * lane + 1] = v.y; sm.tile[r][4 * lane + 2] = v.z; sm.tile[r][4 * lane + 3] = v.w;
+    }
+    __syncthreads();
+
+    float* my = sm.tile[tx];
+#pragma unroll 1
+    for (int b = 0; b < 4; ++b) {
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = my[32 * b + i];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+#pragma unroll
+            for (int j = i + 1; j < 32; ++j) x[j] = fmaf(-x[i], sm.Ud[b][i][j], x[j]);   // computeGauss :132-134, row-wise
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) my[32 * b + i] = x[i];
+#pragma unroll 1
+        for (int j = 32 * (b + 1); j < kNb; j += 4) {
+            float acc0 = my[j], acc1 = my[j + 1], acc2 = my[j + 2], acc3 = my[j + 3];
+#pragma unroll
+            for (int i4 = 0; i4 < 32; i4 += 4) {
+                const float4 u0 = *reinterpret_cast<const float4*>(&sm.Ut[j][32 * b + i4]);
+                const float4 u1 = *reinterpret_cast<const float4*>(&sm.Ut[j + 1][32 * b + i4]);
+                const float4 u2 = *reinterpret_cast<const float4*>(&sm.Ut[j + 2][32 * b + i4]);
+                const float4 u3 = *reinterpret_cast<const float4*>(&sm.Ut[j + 3][32 * b + i4]);
+                acc0 = fmaf(-u0.x, x[i4], acc0); acc0 = fmaf(-u0.y, x[i4 + 1], acc0); acc0 = fmaf(-u0.z, x[i4 + 2], acc0); acc0 = fmaf(-u0.w, x[i4 + 3], acc0);
+                acc1 = fmaf(-u1.x, x[i4], acc1); acc1 = fmaf(-u1.y, x[i4 + 1], acc1); acc1 = fmaf(-u1.z, x[i4 + 2], acc1); acc1 = fmaf(-u1.w, x[i4 + 3], acc1);
+                acc2 = fmaf(-u2.x, x[i4], acc2); acc2 = fmaf(-u2.y, x[i4 + 1], acc2); acc2 = fmaf(-u2.z, x[i4 + 2], acc2); acc2 = fmaf(-u2.w, x[i4 + 3], acc2);
+                acc3 = fmaf(-u3.x, x[i4], acc3); acc3 = fmaf(-u3.y, x[i4 + 1], acc3); acc3 = fmaf(-u3.z, x[i4 + 2], acc3); acc3 = fmaf(-u3.w, x[i4 + 3], acc3);
+            }
+            my[j] = acc0; my[j + 1] = acc1; my[j + 2] = acc2; my[j + 3] = acc3;
+        }
+    }
+    __syncthreads();
+    // write back: in place, plus the TF32 hi/lo split (A-role operand of the trailing update)
+    for (int r = wrp; r < kTileH; r += kTileH / 32) {
+        if (row0 + r >= nrows) break;
+        float4 v = make_float4(sm.tile[r][4 * lane], sm.tile[r][4 * lane + 1], sm.tile[r][4 * lane + 2], sm.tile[r][4 * lane + 3]);
+        *reinterpret_cast<float4*>(a21 + (size_t)(row0 + r) * ld + 4 * lane) = v;
+        if (la_hi != nullptr) {
+            float4 h, l;
+            tf32_split(v.x, h.x, l.x); tf32_split(v.y, h.y, l.y); tf32_split(v.z, h.z, l.z); tf32_split(v.w, h.w, l.w);
+            *reinterpret_cast<float4*>(la_hi + (size_t)(row0 + r) * ldla + k_la + 4 * lane) = h;
+            *reinterpret_cast<float4*>(la_lo + (size_t)(row0 + r) * ldla + k_la + 4 * lane) = l;
+        }
+    }
+}
+
+void launch_lcol(const float* u11, int ldu, float* a21, int ld, int nrows,
+                 float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s)
+{
+    if (nrows <= 0) return;
+    lcol_kernel<<<(nrows + kTileH - 1) / kTileH, kTileH, sizeof(LcolSmem), s>>>(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
+    ++g_launch_count;
+}
+
+// =====================================================================================
+// 4. FP32 FFMA GEMM, NN, row-major: the pure-FFMA variant of the trailing update
+//    (GAUSS_CUDA_MODE_FFMA) and of matmul_cuda.  128x128x16 CTA tile, 256 threads,
+//    8x8 register tile per thread, double-buffered shared memory.
+// =====================================================================================
+constexpr int GBM = 128, GBN = 128, GBK = 16, GAS = GBM + 4;
+
+__global__ void __launch_bounds__(256, 2)
+sgemm_nn_kernel(const float* __restrict__ A, int lda, const float* __restrict__ B, int ldb,
+                float* __restrict__ C, int ldc, int m, int n, int k, float alpha, float beta)
+{
+    __shared__ __align__(16) float As[2][GBK][GAS];   // As[k][m] (transposed on the way in)
+    __shared__ __align__(16) float Bs[2][GBK][GBN];
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const int m0 = blockIdx.y * GBM, n0 = blockIdx.x * GBN;
+
+    // global -> register staging coordinates
+    const int a_r = tid >> 2, a_c = (tid & 3) << 2;          // rows a_r, a_r+64 ; cols a_c..a_c+3
+    const int b_r = tid >> 5, b_c = (tid & 31) << 2;          // rows b_r, b_r+8  ; cols b_c..b_c+3
+    const bool a_ok0 = (m0 + a_r) < m, a_ok1 = (m0 + a_r + 64) < m;
+    const bool b_ok = (n0 + b_c) < n;
+    const float* Ap0 = A + (size_t)(m0 + a_r) * lda + a_c;
+    const float* Ap1 = A + (size_t)(m0 + a_r + 64) * lda + a_c;
+    const float* Bp0 = B + (size_t)b_r * ldb + n0 + b_c;
+    const float* Bp1 = B + (size_t)(b_r + 8) * ldb + n0 + b_c;
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    float4 ra0 = a_ok0 ? *reinterpret_cast<const float4*>(Ap0) : z4;
+    float4 ra1 = a_ok1 ? *reinterpret_cast<const float4*>(Ap1) : z4;
+    float4 rb0 = b_ok ? *reinterpret_cast<const float4*>(Bp0) : z4;
+    float4 rb1 = b_ok ? *reinterpret_cast<const float4*>(Bp1) : z4;
+
+    float acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+    auto stage = [&](int buf) {
+        As[buf][a_c][a_r] = ra0.x; As[buf][a_c + 1][a_r] = ra0.y; As[buf][a_c + 2][a_r] = ra0.z; As[buf][a_c + 3][a_r] = ra0.w;
+        As[buf][a_c][a_r + 64] = ra1.x; As[buf][a_c + 1][a_r + 64] = ra1.y; As[buf][a_c + 2][a_r + 64] = ra1.z; As[buf][a_c + 3][a_r + 64] = ra1.w;
+        *reinterpret_cast<float4*>(&Bs[buf][b_r][b_c]) = rb0;
+        *reinterpret_cast<float4*>(&Bs[buf][b_r + 8][b_c]) = rb1;
+    };
+    stage(0);
+    __syncthreads();
+
+    const int nk = k / GBK;
+    for (int kt = 0; kt < nk; ++kt) {
+        const int buf = kt & 1;
+        if (kt + 1 < nk) {
+            const size_t ao = (size_t)(kt + 1) * GBK;
+            const size_t bo = (size_t)(kt + 1) * GBK * ldb;
+            ra0 = a_ok0 ? *reinterpret_cast<const float4*>(Ap0 + ao) : z4;
+            ra1 = a_ok1 ? *reinterpret_cast<const float4*>(Ap1 + ao) : z4;
+            rb0 = b_ok ? *reinterpret_cast<const float4*>(Bp0 + bo) : z4;
+            rb1 = b_ok ? *reinterpret_cast<const float4*>(Bp1 + bo) : z4;
+        }
+#pragma unroll
+        for (int kk = 0; kk < GBK; ++kk) {
+            const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][kk][ty * 4]);
+            const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][kk][64 + ty * 4]);
+            const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][kk][tx * 4]);
+            const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][kk][64 + tx * 4]);
+            const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        if (kt + 1 < nk) {
+            stage(buf ^ 1);
+            __syncthreads();
+        }
+    }
+
+    // epilogue: C = beta*C + alpha*acc, float4, row/column guarded
+#pragma unroll
+    for (int ih = 0; ih < 2; ++ih)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int r = m0 + ih * 64 + ty * 4 + i;
+            if (r >= m) continue;
+#pragma unroll
+            for (int jh = 0; jh < 2; ++jh) {
+                const int cc = n0 + jh * 64 + tx * 4;
+                if (cc >= n) continue;
+                float* cp = C + (size_t)r * ldc + cc;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (beta != 0.f) v = *reinterpret_cast<const float4*>(cp);
+                const float* ac = acc[ih * 4 + i] + jh * 4;
+                v.x = fmaf(alpha, ac[0], v.x); v.y = fmaf(alpha, ac[1], v.y);
+                v.z = fmaf(alpha, ac[2], v.z); v.w = fmaf(alpha, ac[3], v.w);
+                *reinterpret_cast<float4*>(cp) = v;
+            }
+        }
+}
+
+void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
+                     int m, int n, int k, float alpha, float beta, cudaStream_t s)
+{
+    if (m <= 0 || n <= 0 || k <= 0) return;
+    dim3 grid((n + GBN - 1) / GBN, (m + GBM - 1) / GBM);
+    sgemm_nn_kernel<<<grid, 256, 0, s>>>(A, lda, B, ldb, C, ldc, m, n, k, alpha, beta);
+    ++g_launch_count;
+}
+
+// =====================================================================================
+// 5. Back substitution (solveGauss :144-159), blocked by 128: a one-CTA solve of the
+//    diagonal block, then y[rows above] -= U[rows above, block] * x_block with float4
+//    row reads (each warp streams whole 512 B row segments).
+// =====================================================================================
+constexpr int kTrsvDiagSmem = (kNb * (kNb + 1) + kNb) * (int)sizeof(float);
+
+__global__ void __launch_bounds__(128)
+trsv_diag_kernel(float* __restrict__ ukk, int ld, int ycol, float* __restrict__ x)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float (*U)[kNb + 1] = reinterpret_cast<float (*)[kNb + 1]>(smem_raw);
+    float* xs = reinterpret_cast<float*>(smem_raw) + kNb * (kNb + 1);
+    const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+    for (int r = wrp; r < kNb; r += 4) {
+        const float4 v = *reinterpret_cast<const float4*>(ukk + (size_t)r * ld + 4 * lane);
+        U[r][4 * lane] = v.x; U[r][4 * lane + 1] = v.y; U[r][4 * lane + 2] = v.z; U[r][4 * lane + 3] = v.w;
+    }
+    float y = ukk[(size_t)tid * ld + ycol];       // thread t owns row t of the block
+    __syncthreads();
+    for (int b = 3; b >= 0; --b) {
+        if (wrp == b) {                           // 32x32 triangle: one warp, shuffles only
+            for (int i = 31; i >= 0; --i) {
+                const float xi = __shfl_sync(0xffffffffu, y, i);
+                if (lane < i) y = fmaf(-U[32 * b + lane][32 * b + i], xi, y);
+            }
+            xs[tid] = y;
+        }
+        __syncthreads();
+        if (wrp < b) {                            // rows above: subtract this sub-block's contribution
+#pragma unroll 8
+            for (int i = 0; i < 32; ++i) y = fmaf(-U[tid][32 * b + i], xs[32 * b + i], y);
+        }
+    }
+    x[tid] = y;
+    ukk[(size_t)tid * ld + ycol] = y;
+}
+
+__global__ void __launch_bounds__(256)
+trsv_gemv_kernel(float* __restrict__ u, int ld, int ycol, const float* __restrict__ x, int nrows)
+{
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const float4 xv = *reinterpret_cast<const float4*>(x + 4 * lane);
+    const int r0 = (blockIdx.x * 8 + wrp) * 4;             // 4 rows per warp, 32 rows per CTA
+    float s[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        s[i] = 0.f;
+        if (r0 + i < nrows) {
+            const float4 v = *reinterpret_cast<const float4*>(u + (size_t)(r0 + i) * ld + 4 * lane);
+            s[i] = v.x * xv.x + v.y * xv.y + v.z * xv.z + v.w * xv.w;
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s[i] += __shfl_xor_sync(0xffffffffu, s[i], off);
+    if (lane < 4 && r0 + lane < nrows) {
+        const float mine = lane == 0 ? s[0] : lane == 1 ? s[1] : lane == 2 ? s[2] : s[3];
+        float* yp = u + (size_t)(r0 + lane) * ld + ycol;
+        *yp -= mine;
+    }
+}
+
+void launch_trsv_diag(float* ukk, int ld, int ycol, float* x, cudaStream_t s)
+{
+    trsv_diag_kernel<<<1, 128, kTrsvDiagSmem, s>>>(ukk, ld, ycol, x);
+    ++g_launch_count;
+}
+void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cudaStream_t s)
+{
+    if (nrows <= 0) return;
+    trsv_gemv_kernel<<<(nrows + 31) / 32, 256, 0, s>>>(u, ld, ycol, x, nrows);
+    ++g_launch_count;
+}
+
+// =====================================================================================
+// 6. Layout helpers
+// =====================================================================================
+__global__ void set_column_kernel(float* w, int ld, int col, const float* src, int nrows)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < nrows) w[(size_t)r * ld + col] = src[r];
+}
+__global__ void get_column_kernel(const float* w, int ld, int col, float* dst, int nrows)
+{
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < nrows) dst[r] = w[(size_t)r * ld + col];
+}
+// Rows/columns beyond n are identity: [[A 0][0 I]], rhs 0 -- the padded unknowns come out 0 and
+// never touch the real ones.  One thread per (row, column) of the `width` columns of `nrows` local rows.
+__global__ void pad_identity_kernel(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int width)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y;
+    if (c >= width || r >= nrows) return;
+    const int g = row0_global + r;
+    if (g < n && c < n) return;                   // real matrix entry: leave alone
+    if (g < n && c == width - kPadCols) return;   // real RHS entry
+    w[(size_t)(row0_local + r) * ld + c] = (g >= n && c == g) ? 1.f : 0.f;
+}
+
+void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s)
+{
+    if (nrows <= 0) return;
+    set_column_kernel<<<(nrows + 255) / 256, 256, 0, s>>>(w, ld, col, src, nrows);
+    ++g_launch_count;
+}
+void launch_get_column(const float* w, int ld, int col, float* dst, int nrows, cudaStream_t s)
+{
+    if (nrows <= 0) return;
+    get_column_kernel<<<(nrows + 255) / 256, 256, 0, s>>>(w, ld, col, dst, nrows);
+    ++g_launch_count;
+}
+void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int width, cudaStream_t s)
+{
+    if (nrows <= 0) return;
+    dim3 grid((width + 255) / 256, nrows);
+    pad_identity_kernel<<<grid, 256, 0, s>>>(w, ld, row0_local, row0_global, nrows, n, width);
+    ++g_launch_count;
+}
+
+// ---- matmul operand preparation (tensor-core path) ----
+// hi/lo[r][c] = split(src[r][c]) for r < rows, c < ldd; columns >= cols are zero (K padding).
+__global__ void split_rowmajor_kernel(const float* __restrict__ src, int lds, float* __restrict__ hi, float* __restrict__ lo,
+                                      int ldd, int rows, int cols)
+{
+    const int c4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int r = blockIdx.y;
+    if (c4 >= ldd || r >= rows) return;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) if (c4 + i < cols) v[i] = src[(size_t)r * lds + c4 + i];
+    float4 h, l;
+    tf32_split(v[0], h.x, l.x); tf32_split(v[1], h.y, l.y); tf32_split(v[2], h.z, l.z); tf32_split(v[3], h.w, l.w);
+    *reinterpret_cast<float4*>(hi + (size_t)r * ldd + c4) = h;
+    *reinterpret_cast<float4*>(lo + (size_t)r * ldd + c4) = l;
+}
+// hi/lo[c*ldd + r] = split(src[r][c]) for c < cols, r < rext; rows >= `rows` of the source read as zero.
+// 32x32 tiles through shared memory, both sides coalesced.
+__global__ void split_transpose_kernel(const float* __restrict__ src, int lds, float* __restrict__ hi, float* __restrict__ lo,
+                                       int ldd, int rows, int cols, int rext)
+{
+    __shared__ float t[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;          // 32 x 8
+    for (int i = ty; i < 32; i += 8) {
+        const int r = r0 + i, c = c0 + tx;
+        t[i][tx] = (r < rows && c < cols) ? src[(size_t)r * lds + c] : 0.f;
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i, r = r0 + tx;                 // output row = source column
+        if (c >= cols || r >= rext) continue;
+        float h, l;
+        tf32_split(t[tx][i], h, l);
+        hi[(size_t)c * ldd + r] = h;
+        lo[(size_t)c * ldd + r] = l;
+    }
+}
+void launch_split_rowmajor(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, cudaStream_t s)
+{
+    dim3 grid((ldd / 4 + 127) / 128, rows);
+    split_rowmajor_kernel<<<grid, 128, 0, s>>>(src, lds, hi, lo, ldd, rows, cols);
+    ++g_launch_count;
+}
+void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, int rext, cudaStream_t s)
+{
+    if (cols <= 0 || rext <= 0) return;
+    dim3 grid((cols + 31) / 32, (rext + 31) / 32);
+    split_transpose_kernel<<<grid, dim3(32, 8), 0, s>>>(src, lds, hi, lo, ldd, rows, cols, rext);
+    ++g_launch_count;
+}
+
+// Dynamic shared-memory opt-ins are per device: call once per context with that device current.
+void simt_setup_device()
+{
+    cudaFuncSetAttribute(urow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowSmem));
+    cudaFuncSetAttribute(lcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolSmem));
+    cudaFuncSetAttribute(trsv_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvDiagSmem);
+}
+
+} // namespace gb200

@@ -1,0 +1,372 @@
+// Tensor-core tile engine for sm_100a: C (+)= -/+ (Ahi + Alo) * (Bhi + Blo)^T as split 3xTF32.
+//
+// One persistent CTA per SM, 192 threads, warp-specialised:
+//   warp 0      TMA producer   cp.async.bulk.tensor loads of the four operand tiles of a k-slice
+//                              (A hi/lo: 128 x BK, B hi/lo: 256 x BK, K-major, hardware swizzle)
+//   warp 1      MMA issuer     one elected lane issues tcgen05.mma.kind::tf32, three per 8-wide k step
+//                              (lo*hi, hi*lo, hi*hi - small terms first) into a 128x256 FP32 accumulator
+//                              in TMEM; accumulators are double buffered (2 x 256 columns = all of TMEM)
+//   warps 2..5  epilogue       tcgen05.ld 32 columns at a time -> swizzled smem staging -> TMA
+//                              reduce-add into C (trailing update  A22 -= L21*U12; the MMA negates A)
+//                              or TMA store (matmul, beta = 0)
+// smem ring and TMEM hand-offs use mbarriers; every wait is bounded and traps instead of hanging.
+//
+// It serves both the trailing update of the blocked LU (computeGauss' inner k loop,
+// gauss_internal_input.c:132-134, as a rank-kb update) and matmul_cuda (cuda_matmul.cu:89-101).
+#include "gauss_internal.cuh"
+#include "gauss_cuda.h"
+
+#include <cuda.h>
+#include <stdio.h>
+
+namespace gb200 {
+
+constexpr int TBM = 128;          // tile rows   (UMMA M, cta_group::1)
+constexpr int TBN = 256;          // tile cols   (UMMA N)
+constexpr int TEPI_W = 32;        // epilogue chunk: 32 fp32 columns = one 128 B swizzle row
+constexpr int TSTAGE_C = TBM * TEPI_W * 4;   // 16 KB staging buffer
+constexpr int kTcThreads = 192;
+
+template <int BK, int STAGES>
+struct TcCfg {
+    static constexpr int a_bytes = TBM * BK * 4;
+    static constexpr int b_bytes = TBN * BK * 4;
+    static constexpr int stage_bytes = 2 * a_bytes + 2 * b_bytes;
+    static constexpr int ring_bytes = STAGES * stage_bytes;
+    static constexpr int bar_off = ring_bytes + 2 * TSTAGE_C;
+    static constexpr int smem_bytes = bar_off + 256 + 1024;     // barriers + slack for 1024 B alignment
+    static constexpr int swizzle_bytes = BK * 4;                // 64 or 128
+};
+
+// ---------------------------------------------------------------------------- PTX helpers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// Bounded wait: a protocol bug must surface as a trapped kernel, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > 4000000000LL) {
+            printf("tc_gemm: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n\t.reg .b32 r;\n\t.reg .pred p;\n\t"
+        "elect.sync r|p, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint32_t bar, uint32_t dst, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1)
+{
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* map, uint32_t src, int c0, int c1)
+{
+    asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ void tma_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand tile in shared memory, rows of SWZ bytes, 8-row swizzle atoms (SBO = 8 * SWZ).
+template <int SWZ>
+__device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t saddr)
+{
+    constexpr uint64_t layout = SWZ == 128 ? 2 : (SWZ == 64 ? 4 : 6);
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);               // start address        bits [0,14)
+    d |= (uint64_t)1 << 16;                               // leading byte offset  bits [16,30)  (unused for swizzled K-major)
+    d |= (uint64_t)((8 * SWZ) >> 4) << 32;                // stride byte offset   bits [32,46)
+    d |= (uint64_t)1 << 46;                               // descriptor version   bits [46,48)  (Blackwell)
+    d |= layout << 61;                                    // swizzle mode         bits [61,64)
+    return d;
+}
+
+// ---------------------------------------------------------------------------- the kernel
+template <int BK, int STAGES>
+__global__ void __launch_bounds__(kTcThreads, 1)
+tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant__ CUtensorMap tm_alo,
+               const __grid_constant__ CUtensorMap tm_bhi, const __grid_constant__ CUtensorMap tm_blo,
+               const __grid_constant__ CUtensorMap tm_c,
+               int m, int n, int k, int negate, int reduce)
+{
+    using Cfg = TcCfg<BK, STAGES>;
+    extern __shared__ unsigned char smem_dyn[];
+    const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;      // swizzle atoms need 1024 B alignment
+    const uint32_t bar_base = base + Cfg::bar_off;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    unsigned char* gen_base = smem_dyn + (base - smem_u32(smem_dyn));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int num_n = (n + TBN - 1) / TBN;
+    const int num_tiles = ((m + TBM - 1) / TBM) * num_n;
+    const int num_kb = k / BK;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 4));
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (elect_one()) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+                const int m0 = (t / num_n) * TBM, n0 = (t % num_n) * TBN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty_bar(stage), phase ^ 1);
+                    const uint32_t sa = base + stage * Cfg::stage_bytes;
+                    mbar_expect_tx(full_bar(stage), Cfg::stage_bytes);
+                    tma_load_2d(&tm_ahi, full_bar(stage), sa, kb * BK, m0);
+                    tma_load_2d(&tm_alo, full_bar(stage), sa + Cfg::a_bytes, kb * BK, m0);
+                    tma_load_2d(&tm_bhi, full_bar(stage), sa + 2 * Cfg::a_bytes, kb * BK, n0);
+                    tma_load_2d(&tm_blo, full_bar(stage), sa + 2 * Cfg::a_bytes + Cfg::b_bytes, kb * BK, n0);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (elect_one()) {
+            // instruction descriptor: D=F32, A=B=TF32, both K-major, N=256, M=128, optional negate of A
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((negate ? 1u : 0u) << 13) |
+                                   ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(tempty_bar(as), aphase ^ 1);
+                tc_fence_after();
+                const uint32_t tacc = tmem_base + (uint32_t)(as * TBN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full_bar(stage), phase);
+                    tc_fence_after();
+                    const uint32_t sa = base + stage * Cfg::stage_bytes;
+                    const uint64_t d_ahi = make_kmajor_desc<Cfg::swizzle_bytes>(sa);
+                    const uint64_t d_alo = make_kmajor_desc<Cfg::swizzle_bytes>(sa + Cfg::a_bytes);
+                    const uint64_t d_bhi = make_kmajor_desc<Cfg::swizzle_bytes>(sa + 2 * Cfg::a_bytes);
+                    const uint64_t d_blo = make_kmajor_desc<Cfg::swizzle_bytes>(sa + 2 * Cfg::a_bytes + Cfg::b_bytes);
+#pragma unroll
+                    for (int kk = 0; kk < BK / 8; ++kk) {
+                        const uint64_t adv = (uint64_t)((kk * 32) >> 4);      // 8 tf32 = 32 B along K inside the swizzle row
+                        umma_tf32(tacc, d_alo + adv, d_bhi + adv, idesc, (kb | kk) ? 1u : 0u);
+                        umma_tf32(tacc, d_ahi + adv, d_blo + adv, idesc, 1u);
+                        umma_tf32(tacc, d_ahi + adv, d_bhi + adv, idesc, 1u);
+                    }
+                    umma_commit(empty_bar(stage));          // frees the smem slot when these MMAs retire
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit(tfull_bar(as));                 // accumulator ready for the epilogue
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5, 128 threads) =====================
+        const int q = warp & 3;                             // TMEM lane quarter this warp may touch
+        const int row = q * 32 + lane;
+        const bool issuer = (threadIdx.x == 64);
+        int it = 0;
+        int cbuf = 0;
+        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            const int m0 = (t / num_n) * TBM, n0 = (t % num_n) * TBN;
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            mbar_wait(tfull_bar(as), aphase);
+            tc_fence_after();
+            const int nchunks = min(TBN / TEPI_W, (n - n0 + TEPI_W - 1) / TEPI_W);
+            for (int c = 0; c < nchunks; ++c) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TBN + c * TEPI_W), v);
+                tmem_ld_wait();
+                if (c == nchunks - 1) {                      // all of this accumulator has been read
+                    tc_fence_before();
+                    mbar_arrive(tempty_bar(as));
+                }
+                const uint32_t sbuf = base + Cfg::ring_bytes + cbuf * TSTAGE_C;
+                if (issuer) tma_wait_read<1>();             // the store that last used this buffer has read it
+                named_bar_sync(1, 128);
+                const uint32_t rbase = sbuf + row * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t dst = rbase + ((uint32_t)(j ^ (row & 7)) << 4);     // 128 B swizzle, matches tm_c
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                                 ::"r"(dst), "r"(v[4 * j]), "r"(v[4 * j + 1]), "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
+                }
+                fence_async_smem();
+                named_bar_sync(1, 128);
+                if (issuer) {
+                    if (reduce) tma_reduce_add_2d(&tm_c, sbuf, n0 + c * TEPI_W, m0);
+                    else        tma_store_2d(&tm_c, sbuf, n0 + c * TEPI_W, m0);
+                    tma_commit();
+                }
+                cbuf ^= 1;
+            }
+        }
+        if (issuer) tma_wait_all();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static int g_variant = 0;            // 0: BK=32, 2 stages (128 B swizzle); 1: BK=16, 4 stages (64 B swizzle)
+static int g_num_sms = 0;
+
+bool tc_available()
+{
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return false;
+    if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return false;
+    return major == 10;
+}
+
+int tc_setup_device()
+{
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) return GAUSS_CUDA_CUDA_ERR;
+        g_encode = (EncodeTiledFn)fn;
+    }
+    const char* v = getenv("GAUSS_CUDA_TC_VARIANT");
+    if (v) g_variant = atoi(v) ? 1 : 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<32, 2>::smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_gemm_kernel<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<16, 4>::smem_bytes);
+    return e == cudaSuccess ? GAUSS_CUDA_OK : GAUSS_CUDA_CUDA_ERR;
+}
+
+static int make_map(CUtensorMap* map, const float* ptr, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                    uint32_t box_inner, uint32_t box_outer, CUtensorMapSwizzle swz)
+{
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {ld_elems * sizeof(float)};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)ptr, dims, strides, box, estr,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : (int)cudaErrorInvalidValue;
+}
+
+template <int BK, int STAGES>
+static int launch_variant(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
+                          float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
+{
+    using Cfg = TcCfg<BK, STAGES>;
+    const CUtensorMapSwizzle swz = BK == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    CUtensorMap ta, tal, tb, tbl, tc;
+    int rc = 0;
+    rc |= make_map(&ta, Ahi, k, m, lda, BK, TBM, swz);
+    rc |= make_map(&tal, Alo, k, m, lda, BK, TBM, swz);
+    rc |= make_map(&tb, Bhi, k, n, ldb, BK, TBN, swz);
+    rc |= make_map(&tbl, Blo, k, n, ldb, BK, TBN, swz);
+    rc |= make_map(&tc, C, n, m, ldc, TEPI_W, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return (int)cudaErrorInvalidValue;
+    const int tiles = ((m + TBM - 1) / TBM) * ((n + TBN - 1) / TBN);
+    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
+    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0);
+    ++g_launch_count;
+    return (int)cudaGetLastError();
+}
+
+int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
+               float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
+{
+    if (m <= 0 || n <= 0 || k <= 0) return 0;
+    if (!g_encode || (k % 32) != 0) return (int)cudaErrorInvalidValue;
+    if (g_variant == 1) return launch_variant<16, 4>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
+    return launch_variant<32, 2>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
+}
+
+} // namespace gb200

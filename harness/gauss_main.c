@@ -1,0 +1,146 @@
+/*
+ * gauss_main -- plain-C host harness that keeps the reference program's interface and reaches the
+ * GPU only through include/gauss_cuda.h.
+ *
+ * Interface kept from OpenMP_and_MPI/gauss_openmp/gauss_internal_input.c:
+ *   CLI      -s <size> -t <threads> -h (:171-205)  plus the north_star's positional form  N [seed]
+ *   globals  matrix, B, V, C, swap (:15-16), one contiguous block behind matrix[0] (:27-33)
+ *   calls    allocate_memory, initMatrix | initialize_inputs, computeGauss, solveGauss, in that order
+ *   prints   "\nMatrix Size: %d ; Threads: %d\n" (:207), "Application time: %f Secs\n" (:223),
+ *            VERIFY rows "%6.5f %5.5f\n" of B[i], C[i] (:225-228; here switched on with -v)
+ *   errors   "The matrix is singular\n" on stdout and exit(-1) (:86-89)
+ * The timed window is the reference's: input generation + elimination (+ back substitution).
+ */
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <unistd.h>
+#include <math.h>
+#include <sys/time.h>
+#include "gauss_cuda.h"
+
+double **matrix, *B, *V, *C;
+int *swap;
+static double *X_true;            /* seeded mode only */
+static float *A32, *B32, *X32, *Bafter32;
+static gauss_cuda_ctx *ctx;
+static gauss_cuda_stats stats;
+static int g_mode = GAUSS_CUDA_MODE_3XTF32;
+
+static void die_on(int status, const char *where)
+{
+    if (status == GAUSS_CUDA_OK) return;
+    if (status == GAUSS_CUDA_ZERO_PIVOT) { printf("The matrix is singular\n"); exit(-1); }
+    fprintf(stderr, "%s: %s (%s)\n", where, gauss_cuda_strerror(status), gauss_cuda_last_error());
+    exit(2);
+}
+
+void allocate_memory(int size)
+{
+    size_t n = (size_t)size;
+    double *flat = malloc(n * n * sizeof *flat);
+    matrix = malloc(n * sizeof *matrix);
+    B = malloc(n * sizeof *B); V = malloc(n * sizeof *V); C = malloc(n * sizeof *C);
+    swap = malloc(n * sizeof *swap);
+    A32 = malloc(n * n * sizeof *A32);
+    B32 = malloc(n * sizeof *B32); X32 = malloc(n * sizeof *X32); Bafter32 = malloc(n * sizeof *Bafter32);
+    if (!flat || !matrix || !B || !V || !C || !swap || !A32 || !B32 || !X32 || !Bafter32) { fprintf(stderr, "out of memory\n"); exit(2); }
+    for (size_t r = 0; r < n; ++r) matrix[r] = flat + r * n;
+    die_on(gauss_cuda_init(&ctx, size, 1, 0, g_mode), "gauss_cuda_init");
+}
+
+void initMatrix(int nsize)
+{
+    gauss_host_init_matrix(matrix[0], B, nsize);
+    for (int i = 0; i < nsize; ++i) swap[i] = i;
+}
+
+void initialize_inputs(int nsize, unsigned seed)
+{
+    X_true = malloc((size_t)nsize * sizeof *X_true);
+    gauss_host_initialize_inputs(matrix[0], B, X_true, nsize, seed);
+    for (int i = 0; i < nsize; ++i) { swap[i] = i; C[i] = 0.0; }
+}
+
+/* Forward elimination on the GPU; B comes back as L^-1 b like the reference leaves it. */
+void computeGauss(int nsize)
+{
+    size_t n = (size_t)nsize;
+    for (size_t i = 0; i < n * n; ++i) A32[i] = (float)matrix[0][i];
+    for (size_t i = 0; i < n; ++i) B32[i] = (float)B[i];
+    die_on(gauss_cuda_upload(ctx, A32, B32), "gauss_cuda_upload");
+    die_on(gauss_cuda_compute_gauss(ctx, &stats), "gauss_cuda_compute_gauss");
+}
+
+/* Back substitution into C (the reference's output vector). */
+void solveGauss(int nsize)
+{
+    gauss_cuda_stats bs;
+    die_on(gauss_cuda_solve_gauss(ctx, &bs), "gauss_cuda_solve_gauss");
+    stats.backsub_s = bs.backsub_s;
+    die_on(gauss_cuda_download(ctx, X32, Bafter32), "gauss_cuda_download");
+    for (int i = 0; i < nsize; ++i) { V[i] = C[i] = X32[i]; B[i] = Bafter32[i]; }
+}
+
+void gauss(int nsize) { computeGauss(nsize); solveGauss(nsize); }
+
+static void usage(const char *p)
+{
+    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v]   (reference form)\n"
+           "       %s N [seed]                                               (seeded form)\n"
+           "  -m 0 = tcgen05 3xTF32 (default), 1 = FFMA;  -v prints B[i] C[i] like VERIFY\n", p, p);
+}
+
+int main(int argc, char *argv[])
+{
+    int nsize = 2048, verify = 0, seeded = 0, opt;
+    unsigned seed = 1;
+    while ((opt = getopt(argc, argv, "hs:t:m:v")) != -1) {
+        switch (opt) {
+            case 's': { int s = atoi(optarg); if (s > 0) nsize = s; else fprintf(stderr, "Entered size is negative, hence using the default (%d)\n", 2048); } break;
+            case 't': if (atoi(optarg) <= 0) { fprintf(stderr, "Error: Threads count should be a natural number. \n"); return 0; } break;
+            case 'm': g_mode = atoi(optarg) ? GAUSS_CUDA_MODE_FFMA : GAUSS_CUDA_MODE_3XTF32; break;
+            case 'v': verify = 1; break;
+            case 'h': usage(argv[0]); return 0;
+            default:  usage(argv[0]); return 1;
+        }
+    }
+    if (optind < argc) {                       /* north_star form: N [seed] */
+        int s = atoi(argv[optind]);
+        if (s > 0) nsize = s;
+        seeded = 1;
+        if (optind + 1 < argc) seed = (unsigned)strtoul(argv[optind + 1], NULL, 10);
+    }
+
+    printf("\nMatrix Size: %d ; Threads: %d\n", nsize, 1);
+    allocate_memory(nsize);
+
+    struct timeval t0, t1;
+    gettimeofday(&t0, 0);
+    if (seeded) initialize_inputs(nsize, seed); else initMatrix(nsize);
+    gauss(nsize);
+    gettimeofday(&t1, 0);
+    printf("Application time: %f Secs\n", (double)(t1.tv_sec - t0.tv_sec) + 1e-6 * (double)(t1.tv_usec - t0.tv_usec));
+
+    if (verify) for (int i = 0; i < nsize; ++i) printf("%6.5f %5.5f\n", B[i], C[i]);
+
+    /* extra lines (not in the reference) */
+    const double flop = 2.0 / 3.0 * (double)nsize * nsize * nsize;
+    printf("GPU elimination: %.6f s (%.1f GFLOP/s, 2/3 N^3), back substitution: %.6f s, mode %s, outer block %d\n",
+           stats.factor_s, flop / stats.factor_s * 1e-9, stats.backsub_s,
+           g_mode == GAUSS_CUDA_MODE_FFMA ? "FFMA" : "3xTF32", stats.nb_outer);
+    double err = 0.0;
+    if (seeded) {                              /* the reference's error metric, gauss_external_input.c:246-253 */
+        for (int i = 0; i < nsize; ++i) { double e = fabs((C[i] - X_true[i]) / X_true[i]); if (e > err) err = e; }
+        printf("Error: %e\n", err);
+    } else {                                   /* known answer, gauss_internal_input.c:45-48 */
+        for (int i = 0; i < nsize; ++i) {
+            double want = (i == 0) ? -0.5 : (i == nsize - 1 ? 0.5 : 0.0);
+            if (nsize == 1) want = 0.0;
+            double e = fabs(C[i] - want); if (e > err) err = e;
+        }
+        printf("Known-answer max abs error: %e\n", err);
+    }
+    gauss_cuda_free(ctx);
+    return err <= 1e-3 ? 0 : 3;
+}

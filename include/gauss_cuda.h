@@ -1,0 +1,141 @@
+/*
+ * gauss_cuda.h -- C ABI of the B200-native dense Gaussian-elimination solver and
+ * FP32 matrix multiply (libgauss_cuda.so).  Plain C: pointers, sizes, status codes.
+ *
+ * The reference (svdeepak99/Gaussian_Elimination-CUDA-OpenMP-MPI-Pthreads) has no
+ * library interface: its boundary is a source-level convention -- file-scope
+ * globals plus void functions taking `int nsize`
+ *   (OpenMP_and_MPI/gauss_openmp/gauss_internal_input.c:15-16, :20-43 allocate_memory,
+ *    :50-60 initMatrix, :66-112 getPivot, :118-138 computeGauss, :144-159 solveGauss)
+ * and, for the matrix multiply, one kernel launch on device pointers
+ *   (CUDA_and_OpenMP/Version-2/cuda_matmul.cu:89-101 gpu_matmul, :140-160 host sequence).
+ * Each entry point below names the reference interface it replaces.
+ *
+ * Conventions: every function returns a GAUSS_CUDA_* status and never calls exit();
+ * host buffers are caller-owned; a context owns everything on the device and is not
+ * thread-safe; NULL contexts are rejected (free(NULL) is a no-op).  There is NO CPU
+ * fallback: without a CUDA device every compute call returns GAUSS_CUDA_CUDA_ERR.
+ *
+ * Semantics kept from the reference: no pivoting, the pivot row is normalised so U
+ * has a unit diagonal and L carries the pivots (Crout), B after elimination is
+ * L^-1 b, back substitution has no divisions.  One narrowing: the reference swaps
+ * rows when a pivot is EXACTLY 0.0 (gauss_internal_input.c:75-97); this solver
+ * reports GAUSS_CUDA_ZERO_PIVOT instead, which the harness maps to the reference's
+ * "The matrix is singular" + exit(-1) (gauss_internal_input.c:86-89).
+ */
+#ifndef GAUSS_CUDA_H
+#define GAUSS_CUDA_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gauss_cuda_ctx gauss_cuda_ctx;   /* opaque: device buffers, streams, NCCL communicator */
+
+enum {
+    GAUSS_CUDA_OK         = 0,
+    GAUSS_CUDA_ZERO_PIVOT = 1,   /* a pivot was 0 or non-finite; stats.zero_pivot_row says where */
+    GAUSS_CUDA_BAD_ARG    = 2,
+    GAUSS_CUDA_CUDA_ERR   = 3,   /* see gauss_cuda_last_error() */
+    GAUSS_CUDA_NCCL_ERR   = 4,
+    GAUSS_CUDA_NOT_READY  = 5    /* device-resident call before gauss_cuda_upload */
+};
+
+enum {
+    GAUSS_CUDA_MODE_3XTF32 = 0,  /* trailing update / matmul on tcgen05 tensor cores, split 3xTF32 */
+    GAUSS_CUDA_MODE_FFMA   = 1   /* same algorithm, pure FP32 FFMA kernels (comparison variant) */
+};
+
+typedef struct {
+    double h2d_s, factor_s, backsub_s, d2h_s;   /* CUDA-event times of the last call, seconds */
+    double bcast_bytes;                         /* bytes this rank received over NCCL in the last call */
+    int    zero_pivot_row;                      /* -1, or the global row of the first bad pivot */
+    int    n, n_padded, nb_outer, nb_inner, mode, rank, world;
+    long long kernel_launches;                  /* kernels this library launched in the last call */
+} gauss_cuda_stats;
+
+/* ---- Gaussian elimination ------------------------------------------------------------- */
+
+/* Replaces allocate_memory(size) (gauss_internal_input.c:20-43) for the device side.
+ * n: matrix order (any n >= 1); ngpus: GPUs driven by THIS process (1; the multi-GPU form
+ * is one process per GPU, gauss_cuda_init_dist); nb: outer block, 0 = auto, else a
+ * multiple of 128; mode: GAUSS_CUDA_MODE_*. */
+int gauss_cuda_init(gauss_cuda_ctx **ctx, int n, int ngpus, int nb, int mode);
+
+/* Multi-GPU form, one process per GPU: the reference's MPI row distribution
+ * (OpenMP_and_MPI/gauss_mpi/gauss_internal_input.c:140-155) becomes block-cyclic row
+ * panels (row block r lives on rank r mod world) and its per-step
+ * MPI_Bcast(&matrix[i][i+1], ...) (gauss_mpi/gauss_internal_input.c:137) becomes one NCCL
+ * broadcast of the factored row panel per outer block.  `nccl_id` is 128 bytes obtained
+ * from gauss_cuda_unique_id() on rank 0 and handed to every rank by the launcher
+ * (torch.distributed, MPI, a file ...).  Collective: every rank must call it. */
+int gauss_cuda_unique_id(void *nccl_id_128);
+int gauss_cuda_init_dist(gauss_cuda_ctx **ctx, int n, int rank, int world, int device,
+                         const void *nccl_id_128, int nb, int mode);
+
+/* gauss() of the north_star = initMatrix's data in, computeGauss + solveGauss
+ * (gauss_internal_input.c:118-138, :144-159) on the GPU, X out.
+ *   A      host, row-major n*n, ld = n, not modified (what matrix[0] holds, :30-33);
+ *          in the multi-GPU form every rank passes the same-shaped buffer and only the
+ *          rows it owns are read
+ *   B      host, n                       (the reference's B, :57)
+ *   X      host, n, out                  (the reference's C, :156-158)
+ *   B_out  host, n, out, may be NULL     (B after elimination, printed by VERIFY, :225-228)
+ *   st     may be NULL
+ * Collective in the multi-GPU form. */
+int gauss_cuda_solve(gauss_cuda_ctx *ctx, const float *A, const float *B,
+                     float *X, float *B_out, gauss_cuda_stats *st);
+
+/* Device-resident form, for callers that keep the system in HBM between solves
+ * (and for kernel-only timing): upload once, then each gauss_cuda_solve_resident
+ * restores the working matrix from the resident copy (device-to-device), eliminates
+ * and back-substitutes entirely on the device; download fetches X / B_out. */
+int gauss_cuda_upload(gauss_cuda_ctx *ctx, const float *A, const float *B);
+int gauss_cuda_solve_resident(gauss_cuda_ctx *ctx, gauss_cuda_stats *st);
+int gauss_cuda_download(gauss_cuda_ctx *ctx, float *X, float *B_out);
+
+/* The two halves separately, as the reference exposes them: computeGauss
+ * (gauss_internal_input.c:118-138) then solveGauss (:144-159), on the resident system. */
+int gauss_cuda_compute_gauss(gauss_cuda_ctx *ctx, gauss_cuda_stats *st);
+int gauss_cuda_solve_gauss(gauss_cuda_ctx *ctx, gauss_cuda_stats *st);
+
+/* Reads back the factored matrix (unit-upper U above the diagonal, L with the pivots on
+ * and below it -- the reference zeroes L, gauss_internal_input.c:131, nothing reads it).
+ * LU: host, row-major n*n.  Single-GPU contexts only. */
+int gauss_cuda_download_factors(gauss_cuda_ctx *ctx, float *LU);
+
+void gauss_cuda_free(gauss_cuda_ctx *ctx);
+
+/* ---- FP32 matrix multiply -------------------------------------------------------------- */
+
+/* Replaces the reference's whole timed host sequence cudaMalloc / H2D / gpu_matmul / D2H /
+ * cudaFree (cuda_matmul.cu:135-165).  A, B, C host, row-major n*n.  kernel_s (may be NULL)
+ * receives the device time of the multiply alone. */
+int matmul_cuda(const float *A, const float *B, float *C, int n, int mode, double *kernel_s);
+
+/* Replaces the launch gpu_matmul<<<grid, block>>>(d_A, d_B, d_C, nsize) (cuda_matmul.cu:155,
+ * kernel :89-101): device pointers, C = A*B, asynchronous on `stream` (a cudaStream_t, NULL =
+ * default stream).  Mode 3xTF32 keeps per-device scratch (split operand copies) that is
+ * allocated on first use and grown on demand. */
+int matmul_cuda_device(const float *dA, const float *dB, float *dC, int n, int mode, void *stream);
+
+/* ---- host-side input generators shared with the harness --------------------------------- */
+
+/* initMatrix (gauss_internal_input.c:50-60): A[i][j] = 2*(min(i,j)+1), B[i] = i. */
+void gauss_host_init_matrix(double *A, double *B, int n);
+/* north_star's initialize_inputs(seed): srand(seed); A[i][j] = rand()/32768.0 row-major, the row's
+ * absolute sum added to the diagonal; X_true[i] = i+1; B = A*X_true in double (the reference's
+ * initRHS idea, gauss_openmp/gauss_external_input.c:88-106). */
+void gauss_host_initialize_inputs(double *A, double *B, double *X_true, int n, unsigned seed);
+/* cuda_matmul.cu:126-132: A[idx] = idx+1, B[idx] = 1/(idx+1). */
+void gauss_host_matmul_fill(float *A, float *B, int n);
+
+/* ---- diagnostics ------------------------------------------------------------------------- */
+const char *gauss_cuda_strerror(int status);
+const char *gauss_cuda_last_error(void);     /* text of the last CUDA/NCCL failure in this thread */
+int         gauss_cuda_device_count(void);   /* 0 when no usable CUDA device */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GAUSS_CUDA_H */

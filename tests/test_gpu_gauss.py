@@ -1,0 +1,135 @@
+"""GPU parity of gauss() (computeGauss + solveGauss) against the oracle, through the C ABI.
+
+Tolerances are the north_star's: max |X_gpu - X_ref| / |X_ref| <= 1e-3 (norm-wise on the built-in
+fixture, whose solution has n-2 exact zeros; element-wise in seeded mode) and scaled residual
+||Ax-b||inf / (||A||inf ||x||inf n eps_fp32) <= 10.  The fixture is exact in FP32 and in TF32, so
+there the comparison is bit-exact.
+"""
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from _pkg import pkg
+
+pytestmark = pytest.mark.gpu
+MODES = [pkg.MODE_FFMA, pkg.MODE_3XTF32]
+TOL = 1e-3
+
+
+def fixture_answer(n):
+    x = np.zeros(n, np.float32)
+    if n > 1:
+        x[0], x[-1] = -0.5, 0.5
+    b = np.full(n, 0.5, np.float32)
+    b[0] = 0.0
+    return x, b
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n", [2, 8, 33, 128, 129, 300, 1000, 2048])
+def test_fixture_known_answer_bit_exact(n, mode):
+    # gauss_internal_input.c:45-48 - C = -0.5, 0, ..., 0, 0.5 and B = 0, 0.5, ... for ANY n
+    A, B = pkg.initMatrix(n)
+    X, Bafter = pkg.gauss(A, B, mode=mode, want_b_after=True)
+    wx, wb = fixture_answer(n)
+    assert np.array_equal(X, wx)
+    assert np.array_equal(Bafter, wb)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n,seed", [(64, 1), (200, 2), (512, 3), (1000, 1), (2048, 1)])
+def test_seeded_matches_oracle(n, seed, mode):
+    A, B, Xtrue = pkg.initialize_inputs(n, seed)
+    Xref, Bref, Uref = ol.gauss(A, B, nthreads=8)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        X, Bafter = g.gauss(A, B, want_b_after=True)
+        assert g.stats.zero_pivot_row == -1 and g.stats.kernel_launches > 0
+        LU = g.download_factors()
+    assert ol.max_rel_error(X, Xref) <= TOL
+    assert ol.max_rel_error(Bafter, Bref) <= TOL
+    assert ol.scaled_residual(A, B, X) <= 10.0
+    # unit-upper U: norm-wise against the oracle's (the reference zeroes L, gauss_internal_input.c:131)
+    U = np.triu(LU.astype(np.float64), 1)
+    assert np.max(np.abs(U - np.triu(Uref, 1))) <= TOL * np.max(np.abs(Uref))
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_golden_vectors(golden, mode):
+    for n, seed in ((48, 1), (64, 2), (96, 3)):
+        A, B = golden[f"seed{seed}_n{n}_A"], golden[f"seed{seed}_n{n}_B"]
+        X = pkg.gauss(A, B, mode=mode)
+        assert ol.max_rel_error(X, golden[f"seed{seed}_n{n}_X"]) <= TOL
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("nb", [128, 256, 512])
+def test_outer_block_sizes_agree(nb, mode):
+    n = 1100
+    A, B, Xtrue = pkg.initialize_inputs(n, 5)
+    X = pkg.gauss(A, B, mode=mode, nb=nb)
+    assert ol.max_rel_error(X, Xtrue) <= TOL
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_zero_pivot_reported_as_singular(mode):
+    # the reference would swap rows or print "The matrix is singular" (gauss_internal_input.c:75-97);
+    # the GPU path reports the row instead of swapping (documented narrowing)
+    n = 200
+    A, B, _ = pkg.initialize_inputs(n, 3)
+    A[:, 0] = 0.0
+    with pkg.GaussCuda(n, mode=mode) as g:
+        with pytest.raises(pkg.SingularMatrix):
+            g.gauss(A, B)
+        assert g.stats.zero_pivot_row == 0
+    A, B, _ = pkg.initialize_inputs(n, 3)
+    A[150, :] = A[149, :]                      # exact zero appears at pivot 150 during elimination
+    with pkg.GaussCuda(n, mode=pkg.MODE_FFMA) as g:
+        try:
+            g.gauss(A, B)
+            hit = g.stats.zero_pivot_row
+        except pkg.SingularMatrix:
+            hit = g.stats.zero_pivot_row
+        assert hit in (-1, 150)                # rounding may leave a tiny non-zero pivot
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_resident_api_equals_host_api(mode):
+    n = 700
+    A, B, _ = pkg.initialize_inputs(n, 8)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        X1 = g.gauss(A, B)
+        g.upload(A, B)
+        with pytest.raises(pkg.GaussCudaError):
+            g.solveGauss()                     # nothing factored yet
+        g.computeGauss()
+        assert g.stats.factor_s > 0
+        g.solveGauss()
+        X2, B2 = g.download(want_b_after=True)
+        g.solve_resident()                     # restores the pristine copy: repeatable
+        X3 = g.download()
+    assert np.array_equal(X1, X2) and np.array_equal(X2, X3)
+    assert ol.max_rel_error(B2, ol.gauss(A, B)[1]) <= TOL
+
+
+def test_solve_before_upload_is_rejected():
+    with pkg.GaussCuda(64, mode=pkg.MODE_FFMA) as g:
+        with pytest.raises(pkg.GaussCudaError) as e:
+            g.solve_resident()
+        assert e.value.status == pkg.NOT_READY
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_linearity_and_residual_at_scale(mode):
+    # size-independent properties at a size the CPU oracle would take minutes for
+    n = 8192
+    rng = np.random.default_rng(11)
+    A = rng.random((n, n), dtype=np.float32)
+    A[np.arange(n), np.arange(n)] += A.sum(axis=1)
+    xt = np.arange(1, n + 1, dtype=np.float64)
+    B = (A.astype(np.float64) @ xt).astype(np.float32)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        X = g.gauss(A, B)
+        X2 = g.gauss(A, 2.0 * B)
+    assert ol.max_rel_error(X, xt) <= TOL
+    assert ol.scaled_residual(A, B, X) <= 10.0
+    assert np.max(np.abs(X2 - 2.0 * X)) <= 1e-5 * np.max(np.abs(X2))       # scaling b by 2 is exact in binary FP
