@@ -42,6 +42,7 @@ class GaussStats(C.Structure):
         ("n", C.c_int), ("n_padded", C.c_int), ("nb_outer", C.c_int), ("nb_inner", C.c_int),
         ("mode", C.c_int), ("rank", C.c_int), ("world", C.c_int),
         ("kernel_launches", C.c_longlong),
+        ("update_s", C.c_double), ("update_flops", C.c_double), ("update_launches", C.c_int),
     ]
 
     def asdict(self):

@@ -137,6 +137,9 @@ struct gauss_cuda_ctx {
     int* status = nullptr;   // device: 0 or (row+1) of the first bad pivot
     cudaStream_t s_main = nullptr;
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    std::vector<cudaEvent_t> upd_ev;    // 2 per outer block: brackets of the trailing-update launches
+    std::vector<double> upd_flops;
+    int upd_count = 0;
     ncclComm_t comm = nullptr;
     bool resident = false, factored = false;
     double bcast_bytes = 0.0;
@@ -205,6 +208,9 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
     for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    c->upd_ev.assign(2 * (size_t)c->nblk, nullptr);
+    c->upd_flops.assign((size_t)c->nblk, 0.0);
+    for (size_t i = 0; i < c->upd_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->upd_ev[i]);
     if (e != cudaSuccess) { int rc = cuda_fail(e, "context allocation", __LINE__); gauss_cuda_free(c); return rc; }
 
     if (world > 1) {
@@ -247,6 +253,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     for (float* b : bufs) if (b) cudaFree(b);
     if (c->status) cudaFree(c->status);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : c->upd_ev) if (e) cudaEventDestroy(e);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     delete c;
 }
@@ -269,9 +276,9 @@ static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const floa
                                  (size_t)n * sizeof(float), real, cudaMemcpyHostToDevice, s));
             launch_set_column(dst + (size_t)l0 * c->ld, c->ld, c->np, c->hvec + g0, real, s);
             // columns [n, ld) of real rows except the RHS column
-            launch_pad_identity(dst, c->ld, l0, g0, real, n, c->ld, s);
+            launch_pad_identity(dst, c->ld, l0, g0, real, n, n, s);
         }
-        if (rows > real) launch_pad_identity(dst, c->ld, l0 + real, g0 + real, rows - real, n, c->ld, s);
+        if (rows > real) launch_pad_identity(dst, c->ld, l0 + real, g0 + real, rows - real, n, 0, s);
     }
     CK(cudaGetLastError());
     return GAUSS_CUDA_OK;
@@ -301,6 +308,7 @@ static int factor(gauss_cuda_ctx* c)
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     CK(cudaMemsetAsync(c->status, 0, sizeof(int), s));
     c->bcast_bytes = 0.0;
+    c->upd_count = 0;
     for (int K = 0; K < c->nblk; ++K) {
         const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
         const int ninner = kb / kNb;
@@ -367,11 +375,16 @@ static int factor(gauss_cuda_ctx* c)
                     if (rc) return rc;
                 }
             }
+            const int ui = c->upd_count;
+            CK(cudaEventRecord(c->upd_ev[2 * ui], s));
             int rc = gemm_update(c, Wb + k0, ld, Pn + kb, ldp,
                                  c->la_hi ? c->la_hi + (size_t)l0 * NB : nullptr, c->la_lo ? c->la_lo + (size_t)l0 * NB : nullptr,
                                  c->ub_hi ? c->ub_hi + (size_t)(k0 + kb) * NB : nullptr, c->ub_lo ? c->ub_lo + (size_t)(k0 + kb) * NB : nullptr,
                                  Wb + k0 + kb, mbelow, ld - (k0 + kb), kb);
             if (rc) return rc;
+            CK(cudaEventRecord(c->upd_ev[2 * ui + 1], s));
+            c->upd_flops[ui] = 2.0 * (double)mbelow * (double)(np + 1 - (k0 + kb)) * (double)kb;
+            c->upd_count = ui + 1;
         }
     }
     CK(cudaGetLastError());
@@ -425,6 +438,17 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
     o.zero_pivot_row = flag ? flag - 1 : -1;
     o.n = c->n; o.n_padded = c->np; o.nb_outer = c->NB; o.nb_inner = kNb; o.mode = c->mode; o.rank = c->rank; o.world = c->world;
     o.kernel_launches = g_launch_count;
+    o.update_s = 0.0; o.update_flops = 0.0; o.update_launches = 0;
+    if (fac) {
+        for (int i = 0; i < c->upd_count; ++i) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, c->upd_ev[2 * i], c->upd_ev[2 * i + 1]) == cudaSuccess) {
+                o.update_s += (double)ms * 1e-3;
+                o.update_flops += c->upd_flops[i];
+                o.update_launches += 1;
+            }
+        }
+    }
     if (st) *st = o;
     return flag ? GAUSS_CUDA_ZERO_PIVOT : GAUSS_CUDA_OK;
 }

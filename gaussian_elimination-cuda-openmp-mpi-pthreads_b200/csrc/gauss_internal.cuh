@@ -44,7 +44,7 @@ void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cud
 // Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.
 void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s);
 void launch_get_column(const float* w, int ld, int col, float* dst, int nrows, cudaStream_t s);
-void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int width, cudaStream_t s);
+void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int col0, cudaStream_t s);
 
 // matmul operand preparation for the tensor-core path: A -> hi/lo (row-major), B -> hi/lo transposed.
 void launch_split_rowmajor(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, cudaStream_t s);

@@ -82,7 +82,9 @@ diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__
 {
     __shared__ float rowbuf[2][kNb];
     __shared__ float colbuf[2][kNb];
+    __shared__ int first_bad;
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5;
+    if (tid == 0) first_bad = kNb;
     float a[8][8];
 #pragma unroll
     for (int p = 0; p < 8; ++p)
@@ -101,7 +103,10 @@ diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__
     for (int p = 0; p < 8; ++p)
 #pragma unroll
         for (int q = 0; q < 8; ++q) blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q] = a[p][q];
-    if (bad >= 0) atomicCAS(status, 0, grow0 + bad + 1);
+    // earliest bad pivot of this block; the first block to report wins (blocks run in pivot order)
+    if (bad >= 0) atomicMin(&first_bad, bad);
+    __syncthreads();
+    if (tid == 0 && first_bad < kNb) atomicCAS(status, 0, grow0 + first_bad + 1);
 }
 
 void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s)
@@ -494,15 +499,15 @@ __global__ void get_column_kernel(const float* w, int ld, int col, float* dst, i
     if (r < nrows) dst[r] = w[(size_t)r * ld + col];
 }
 // Rows/columns beyond n are identity: [[A 0][0 I]], rhs 0 -- the padded unknowns come out 0 and
-// never touch the real ones.  One thread per (row, column) of the `width` columns of `nrows` local rows.
-__global__ void pad_identity_kernel(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int width)
+// never touch the real ones.  One thread per (row, column) over columns [col0, ld) of `nrows` local rows;
+// real matrix entries and real RHS entries (column ld - kPadCols) are left alone.
+__global__ void pad_identity_kernel(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int col0)
 {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = col0 + blockIdx.x * blockDim.x + threadIdx.x;
     const int r = blockIdx.y;
-    if (c >= width || r >= nrows) return;
+    if (c >= ld || r >= nrows) return;
     const int g = row0_global + r;
-    if (g < n && c < n) return;                   // real matrix entry: leave alone
-    if (g < n && c == width - kPadCols) return;   // real RHS entry
+    if (g < n && (c < n || c == ld - kPadCols)) return;
     w[(size_t)(row0_local + r) * ld + c] = (g >= n && c == g) ? 1.f : 0.f;
 }
 
@@ -518,11 +523,11 @@ void launch_get_column(const float* w, int ld, int col, float* dst, int nrows, c
     get_column_kernel<<<(nrows + 255) / 256, 256, 0, s>>>(w, ld, col, dst, nrows);
     ++g_launch_count;
 }
-void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int width, cudaStream_t s)
+void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int col0, cudaStream_t s)
 {
-    if (nrows <= 0) return;
-    dim3 grid((width + 255) / 256, nrows);
-    pad_identity_kernel<<<grid, 256, 0, s>>>(w, ld, row0_local, row0_global, nrows, n, width);
+    if (nrows <= 0 || col0 >= ld) return;
+    dim3 grid((ld - col0 + 255) / 256, nrows);
+    pad_identity_kernel<<<grid, 256, 0, s>>>(w, ld, row0_local, row0_global, nrows, n, col0);
     ++g_launch_count;
 }
 

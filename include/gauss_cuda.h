@@ -52,6 +52,10 @@ typedef struct {
     int    zero_pivot_row;                      /* -1, or the global row of the first bad pivot */
     int    n, n_padded, nb_outer, nb_inner, mode, rank, world;
     long long kernel_launches;                  /* kernels this library launched in the last call */
+    /* the dominant kernel (trailing update A22 -= L21*U12, one launch per outer block), timed with CUDA
+     * events on the library's stream: summed duration, algorithmic flops (2*m*n*k per launch), launches */
+    double update_s, update_flops;
+    int    update_launches;
 } gauss_cuda_stats;
 
 /* ---- Gaussian elimination ------------------------------------------------------------- */

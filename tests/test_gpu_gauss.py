@@ -5,6 +5,8 @@ fixture, whose solution has n-2 exact zeros; element-wise in seeded mode) and sc
 ||Ax-b||inf / (||A||inf ||x||inf n eps_fp32) <= 10.  The fixture is exact in FP32 and in TF32, so
 there the comparison is bit-exact.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -12,7 +14,8 @@ import oracle_lib as ol
 from _pkg import pkg
 
 pytestmark = pytest.mark.gpu
-MODES = [pkg.MODE_FFMA, pkg.MODE_3XTF32]
+_sel = os.environ.get("GAUSS_TEST_MODES", "all")          # bring-up aid: ffma | tc | all
+MODES = [m for m, tag in ((pkg.MODE_FFMA, "ffma"), (pkg.MODE_3XTF32, "tc")) if _sel in ("all", tag)]
 TOL = 1e-3
 
 
@@ -125,11 +128,14 @@ def test_linearity_and_residual_at_scale(mode):
     rng = np.random.default_rng(11)
     A = rng.random((n, n), dtype=np.float32)
     A[np.arange(n), np.arange(n)] += A.sum(axis=1)
-    xt = np.arange(1, n + 1, dtype=np.float64)
+    # preset solution of bounded dynamic range: an ELEMENT-wise 1e-3 on x = 1..n would demand
+    # |dx| <= 1e-3 next to entries of size n, i.e. 1e-7 * ||x||, which no FP32 solver can promise
+    xt = 1.0 + (np.arange(n) % 8) * 0.125
     B = (A.astype(np.float64) @ xt).astype(np.float32)
     with pkg.GaussCuda(n, mode=mode) as g:
         X = g.gauss(A, B)
         X2 = g.gauss(A, 2.0 * B)
+    print("n", n, "mode", mode, "max rel err", ol.max_rel_error(X, xt), "scaled residual", ol.scaled_residual(A, B, X))
     assert ol.max_rel_error(X, xt) <= TOL
     assert ol.scaled_residual(A, B, X) <= 10.0
     assert np.max(np.abs(X2 - 2.0 * X)) <= 1e-5 * np.max(np.abs(X2))       # scaling b by 2 is exact in binary FP
