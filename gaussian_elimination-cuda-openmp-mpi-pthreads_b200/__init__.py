@@ -28,7 +28,7 @@ ABI_SYMBOLS = (
     "gauss_cuda_init", "gauss_cuda_unique_id", "gauss_cuda_init_dist", "gauss_cuda_solve",
     "gauss_cuda_upload", "gauss_cuda_solve_resident", "gauss_cuda_download",
     "gauss_cuda_compute_gauss", "gauss_cuda_solve_gauss", "gauss_cuda_download_factors",
-    "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device",
+    "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device", "matmul_cuda_device_noalloc",
     "gauss_host_init_matrix", "gauss_host_initialize_inputs", "gauss_host_matmul_fill",
     "gauss_cuda_strerror", "gauss_cuda_last_error", "gauss_cuda_device_count",
 )
@@ -88,6 +88,7 @@ def lib():
         L.gauss_cuda_free.restype = None
         L.matmul_cuda.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, _dp]
         L.matmul_cuda_device.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp]
+        L.matmul_cuda_device_noalloc.argtypes = [vp, vp, vp, C.c_int, C.c_int, vp]
         L.gauss_host_init_matrix.argtypes = [_dp, _dp, C.c_int]
         L.gauss_host_init_matrix.restype = None
         L.gauss_host_initialize_inputs.argtypes = [_dp, _dp, _dp, C.c_int, C.c_uint]
@@ -315,3 +316,15 @@ def matmul_cuda_device(dA, dB, dC, n, mode=MODE_3XTF32, stream=None):
     """Device pointers (ints, e.g. torch.Tensor.data_ptr()): replaces gpu_matmul<<<...>>> (cuda_matmul.cu:155)."""
     _check(lib().matmul_cuda_device(C.c_void_p(dA), C.c_void_p(dB), C.c_void_p(dC), n, mode,
                                     C.c_void_p(stream) if stream else None))
+
+
+NOALLOC_MAX_N = 1024
+
+
+def matmul_cuda_device_noalloc(dA, dB, dC, n, mode=MODE_3XTF32, stream=None):
+    """matmul_cuda_device for hosts that must not allocate device memory after start-up (fixed memory
+    budgets, latency-bound loops): the scratch is a 20 MiB array built into the library, so n <= 1024.
+    The first call per device does a one-time set-up; calls that may overlap on the GPU must be serialised
+    by the caller because they share that array."""
+    _check(lib().matmul_cuda_device_noalloc(C.c_void_p(dA), C.c_void_p(dB), C.c_void_p(dC), n, mode,
+                                            C.c_void_p(stream) if stream else None))

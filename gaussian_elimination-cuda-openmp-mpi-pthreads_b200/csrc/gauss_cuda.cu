@@ -713,3 +713,55 @@ extern "C" int matmul_cuda(const float* A, const float* B, float* C, int n, int 
     if (e != cudaSuccess) return cuda_fail(e, "matmul_cuda copies", __LINE__);
     return GAUSS_CUDA_OK;
 }
+
+// ------------------------------------------------------------------------------------------
+// matmul for callers that may not allocate
+// ------------------------------------------------------------------------------------------
+// Some hosts cannot let a library call cudaMalloc: an application that sized its device memory at
+// start-up and forbids driver allocations afterwards (a late cudaMalloc can fail under memory
+// pressure and it synchronises the whole device), or a latency-bound loop that must not block.
+// For them the scratch of the multiply lives in the array below instead of a cudaMalloc'd buffer.
+// It is part of the library image: EVERY GPU that loads libgauss_cuda.so carries these 20 MiB
+// until the process exits, whether or not the entry point is ever called.
+constexpr int    kNoAllocMaxN = 1024;
+constexpr size_t kNoAllocFloats = 5u * 1024u * 1024u;               // 4 split operand copies + one padded C, n <= 1024
+static __device__ __align__(256) float g_noalloc_scratch[kNoAllocFloats];
+
+// In host code `g_noalloc_scratch` is only a handle; the device address has to be asked for, once per
+// device, with that device current.  Cached here after the first successful query.
+static float* g_noalloc_addr[16] = {nullptr};
+
+extern "C" int matmul_cuda_device_noalloc(const float* dA, const float* dB, float* dC, int n, int mode, void* stream)
+{
+    if (!dA || !dB || !dC || n < 1) return GAUSS_CUDA_BAD_ARG;
+    if (mode != GAUSS_CUDA_MODE_3XTF32 && mode != GAUSS_CUDA_MODE_FFMA) return GAUSS_CUDA_BAD_ARG;
+    if (n > kNoAllocMaxN) {
+        snprintf(g_err, sizeof g_err, "matmul_cuda_device_noalloc: n = %d exceeds the built-in scratch (n <= %d); "
+                 "use matmul_cuda_device, which allocates", n, kNoAllocMaxN);
+        return GAUSS_CUDA_BAD_ARG;
+    }
+    if (gauss_cuda_device_count() < 1) { snprintf(g_err, sizeof g_err, "no CUDA device (no CPU fallback)"); return GAUSS_CUDA_CUDA_ERR; }
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 16) return GAUSS_CUDA_BAD_ARG;
+    if (matmul_scratch_bytes(n, mode) > kNoAllocFloats * sizeof(float)) return GAUSS_CUDA_BAD_ARG;   // cannot happen for n <= 1024
+    if (!g_noalloc_addr[dev]) {
+        // first call on this device: one-time set-up (symbol address, kernel attributes, TMA encoder)
+        float* p = nullptr;
+        CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        simt_setup_device();
+        if (mode == GAUSS_CUDA_MODE_3XTF32 || tc_available()) {
+            int rc = tc_setup_device();
+            if (rc) return rc;
+        }
+        g_noalloc_addr[dev] = p;
+    }
+    if (mode == GAUSS_CUDA_MODE_3XTF32 && !tc_available()) {
+        snprintf(g_err, sizeof g_err, "GAUSS_CUDA_MODE_3XTF32 needs an sm_100 device");
+        return GAUSS_CUDA_CUDA_ERR;
+    }
+    // Every region of the scratch that this call reads is written by this call first (the operand
+    // splits include their zero K-padding; the padded FFMA path clears its operand copies), so the
+    // previous call's contents never leak into the result.
+    return matmul_on_device(dA, dB, dC, n, mode, g_noalloc_addr[dev], (cudaStream_t)stream);
+}

@@ -123,6 +123,23 @@ int matmul_cuda(const float *A, const float *B, float *C, int n, int mode, doubl
  * allocated on first use and grown on demand. */
 int matmul_cuda_device(const float *dA, const float *dB, float *dC, int n, int mode, void *stream);
 
+/* Same multiply for callers that are not allowed to allocate device memory.  (No counterpart in the
+ * reference, which cudaMallocs inside its timed window, cuda_matmul.cu:142-146.)  Think of a host
+ * application that carved up the GPU's memory at start-up and forbids cudaMalloc afterwards, or a
+ * latency-bound loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply.
+ * This entry point calls no cudaMalloc, cudaFree or allocating library routine: its scratch is a fixed
+ * 20 MiB array inside the library image, present on every GPU that loads libgauss_cuda.so until the
+ * process exits.
+ *   limit     n <= 1024; larger n returns GAUSS_CUDA_BAD_ARG (gauss_cuda_last_error() says why)
+ *   set-up    the FIRST call on each device looks up the array's device address and sets kernel
+ *             attributes; make that first call with the device current and before any stream capture
+ *   sharing   all calls on a device use the same array, which keeps the previous call's contents;
+ *             each call rewrites what it reads, so results do not depend on earlier calls, but two
+ *             calls whose kernels can overlap on the GPU (different streams, no dependency) RACE on
+ *             it -- serialise them
+ * Arguments and result are those of matmul_cuda_device. */
+int matmul_cuda_device_noalloc(const float *dA, const float *dB, float *dC, int n, int mode, void *stream);
+
 /* ---- host-side input generators shared with the harness --------------------------------- */
 
 /* initMatrix (gauss_internal_input.c:50-60): A[i][j] = 2*(min(i,j)+1), B[i] = i. */
