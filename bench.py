@@ -36,6 +36,15 @@ WORKLOADS = {
     "gauss2048": ("gauss", 2048),
     "matmul2048": ("matmul", 2048),
 }
+_REAL_STDOUT = None
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 METRIC = "gauss_elim_gflops"
 UNIT = "GFLOP/s"
 
@@ -180,7 +189,7 @@ def reference_arm(args, rank):
     for i in range(args.warmup + args.steps):
         t = run_reference_cpu(nsample, cores)
         if t is None:
-            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/gauss_internal_input not built"}))
+            emit({"impl": "reference", "unavailable": "oracle/_ref/gauss_internal_input not built"})
             return
         if i >= args.warmup:
             times.append(t)
@@ -193,7 +202,7 @@ def reference_arm(args, rank):
             "cpu_baseline": {"value": gf, "unit": UNIT, "cores": cores, "kind": "reference",
                              "sample": f"gauss_internal_input -s {nsample} -t {cores}, its own Application time window"},
             "e2e": {"value": gf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------
@@ -217,6 +226,12 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    # stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version banner, ...)
+    # is sent to stderr instead, and the real stdout is kept aside for the final line
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     if args.impl == "reference":
         reference_arm(args, rank)
@@ -358,7 +373,7 @@ def main():
                 "factor_only_gflops": flop / (fac_s / args.steps) * 1e-9,
                 "max_rel_err": max_rel_err,
                 "gpu_launches": total_launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks}
-        print(json.dumps(line))
+        emit(line)
     g.close()
     if world > 1:
         dist.destroy_process_group()
@@ -416,7 +431,7 @@ def bench_matmul(args, pkg, n, mode, peaks, peak_src, cores, rank):
             "roofline": {"bound": "tensor", "achieved": value * 1e-3, "peak": tf32x3, "unit": "TFLOP/s", "frac": value * 1e-3 / tf32x3,
                          "traffic": None, "peak_basis": f"{peak_src} bf16_tflops_sustained / 6", "note": "includes the two operand split/transposes"},
             "reference_kernel_ms_on_this_gpu": ref_ms, "clocks": clocks}
-    print(json.dumps(line))
+    emit(line)
 
 
 if __name__ == "__main__":

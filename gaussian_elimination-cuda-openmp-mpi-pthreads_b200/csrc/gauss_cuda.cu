@@ -129,13 +129,15 @@ struct gauss_cuda_ctx {
     int rows_local = 0;      // rows of W held by this rank (multiple of 128)
     float* W = nullptr;      // working augmented matrix  [rows_local x ld]
     float* W0 = nullptr;     // resident pristine copy (gauss_cuda_upload), same shape
-    float* pbuf = nullptr;   // packed row panel [NB x ld]                      (world > 1)
+    float* pbuf[2] = {nullptr, nullptr};   // packed row panels [NB x ld], double buffered   (world > 1)
     float* la_hi = nullptr, *la_lo = nullptr;   // [rows_local x NB]  split L operand (3xTF32 mode)
-    float* ub_hi = nullptr, *ub_lo = nullptr;   // [ld x NB]          split U operand, transposed
+    float* ub_hi[2] = {nullptr, nullptr};       // [ld x NB]          split U operand, transposed;
+    float* ub_lo[2] = {nullptr, nullptr};       //                    second copy only when world > 1 (look-ahead)
     float* xvec = nullptr;   // [np] solution
     float* hvec = nullptr;   // [np] staging for RHS upload / B_out
     int* status = nullptr;   // device: 0 or (row+1) of the first bad pivot
-    cudaStream_t s_main = nullptr;
+    cudaStream_t s_main = nullptr, s_comm = nullptr;
+    cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> upd_ev;    // 2 per outer block: brackets of the trailing-update launches
     std::vector<double> upd_flops;
@@ -197,19 +199,29 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     A((void**)&c->xvec, (size_t)c->np * sizeof(float));
     A((void**)&c->hvec, (size_t)c->np * sizeof(float));
     A((void**)&c->status, sizeof(int));
-    if (world > 1) A((void**)&c->pbuf, (size_t)c->NB * c->ld * sizeof(float));
+    if (world > 1) for (int i = 0; i < 2; ++i) A((void**)&c->pbuf[i], (size_t)c->NB * c->ld * sizeof(float));
     if (mode == GAUSS_CUDA_MODE_3XTF32) {
         const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
         const size_t ub = (size_t)c->ld * c->NB * sizeof(float);
         A((void**)&c->la_hi, la); A((void**)&c->la_lo, la);
-        A((void**)&c->ub_hi, ub); A((void**)&c->ub_lo, ub);
-        if (e == cudaSuccess) e = cudaMemset(c->ub_hi, 0, ub);
-        if (e == cudaSuccess) e = cudaMemset(c->ub_lo, 0, ub);
+        for (int i = 0; i < (world > 1 ? 2 : 1); ++i) {
+            A((void**)&c->ub_hi[i], ub); A((void**)&c->ub_lo[i], ub);
+            if (e == cudaSuccess) e = cudaMemset(c->ub_hi[i], 0, ub);
+            if (e == cudaSuccess) e = cudaMemset(c->ub_lo[i], 0, ub);
+        }
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
+    if (world > 1) {
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_comm, cudaStreamNonBlocking);
+        for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+            e = cudaEventCreateWithFlags(&c->ev_ready[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_free[i], cudaEventDisableTiming);
+        }
+    }
     for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
-    c->upd_ev.assign(2 * (size_t)c->nblk, nullptr);
-    c->upd_flops.assign((size_t)c->nblk, 0.0);
+    c->upd_ev.assign(4 * (size_t)c->nblk, nullptr);            // look-ahead splits some updates in two launches
+    c->upd_flops.assign(2 * (size_t)c->nblk, 0.0);
     for (size_t i = 0; i < c->upd_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->upd_ev[i]);
     if (e != cudaSuccess) { int rc = cuda_fail(e, "context allocation", __LINE__); gauss_cuda_free(c); return rc; }
 
@@ -249,11 +261,18 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     cudaSetDevice(c->device);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
-    float* bufs[] = {c->W, c->W0, c->pbuf, c->la_hi, c->la_lo, c->ub_hi, c->ub_lo, c->xvec, c->hvec};
+    if (c->s_comm) cudaStreamSynchronize(c->s_comm);
+    float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi, c->la_lo, c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
     if (c->status) cudaFree(c->status);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->upd_ev) if (e) cudaEventDestroy(e);
+    for (int i = 0; i < 2; ++i) {
+        if (c->ev_ready[i]) cudaEventDestroy(c->ev_ready[i]);
+        if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+        if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
+    }
+    if (c->s_comm) cudaStreamDestroy(c->s_comm);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     delete c;
 }
@@ -301,92 +320,194 @@ static int gemm_update(gauss_cuda_ctx* c, const float* A, int lda, const float* 
     return GAUSS_CUDA_OK;
 }
 
-static int factor(gauss_cuda_ctx* c)
+// ---- the pieces of one outer step --------------------------------------------------------
+struct PanelRef {            // where the factored row panel of the current outer block can be read
+    const float* p;          // element (panel row 0, column k0)
+    int ld;
+    float* ub_hi; float* ub_lo;     // split, transposed U operand of this step (3xTF32 mode)
+};
+
+// P1: factor the row panel of outer block K in place on its owner.
+static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo)
 {
     cudaStream_t s = c->s_main;
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
-    CK(cudaMemsetAsync(c->status, 0, sizeof(int), s));
-    c->bcast_bytes = 0.0;
-    c->upd_count = 0;
-    for (int K = 0; K < c->nblk; ++K) {
-        const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
-        const int ninner = kb / kNb;
-        const bool mine = owner == c->rank;
-        float* P = mine ? c->W + (size_t)blk_local_row(c, K) * ld : nullptr;     // the row panel, in place
-        const int lrow = mine ? blk_local_row(c, K) : 0;
-        // ---- P1: factor the row panel on its owner
-        if (mine) {
-            for (int j = 0; j < ninner; ++j) {
-                const int kk = k0 + j * kNb, r = j * kNb;
-                launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
-                launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
-                            tc ? c->ub_hi + (size_t)(kk + kNb) * NB : nullptr, tc ? c->ub_lo + (size_t)(kk + kNb) * NB : nullptr,
-                            NB, r, s);
-                const int mrem = kb - (r + kNb);
-                if (mrem > 0) {
-                    launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
-                                tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB : nullptr,
-                                NB, r, s);
-                    int rc = gemm_update(c, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
-                                         tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
-                                         tc ? c->ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? c->ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
-                                         P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
-                    if (rc) return rc;
-                }
-            }
-        }
-        // ---- broadcast the factored row panel (the reference's MPI_Bcast of the pivot row, gauss_mpi :137)
-        const float* Pn = P + (mine ? k0 : 0);    // panel origin = element (row k0, col k0)
-        int ldp = ld;
-        if (c->world > 1) {
-            ldp = ld - k0;
-            if (mine)
-                CK(cudaMemcpy2DAsync(c->pbuf, (size_t)ldp * sizeof(float), P + k0, (size_t)ld * sizeof(float),
-                                     (size_t)ldp * sizeof(float), kb, cudaMemcpyDeviceToDevice, s));
-            NK(g_nccl.Broadcast(c->pbuf, c->pbuf, (size_t)kb * ldp, ncclFloat, owner, c->comm, s));
-            if (!mine) c->bcast_bytes += (double)kb * ldp * sizeof(float);
-            Pn = c->pbuf;
-            if (tc && !mine) {
-                // rebuild the split, transposed U operand from the raw panel: columns right of each inner block
-                for (int j = 0; j < ninner; ++j) {
-                    const int r = j * kNb, cfirst = r + kNb;          // panel-relative first column
-                    launch_split_transpose(Pn + (size_t)r * ldp + cfirst, ldp,
-                                           c->ub_hi + (size_t)(k0 + cfirst) * NB + r, c->ub_lo + (size_t)(k0 + cfirst) * NB + r,
-                                           NB, kNb, ldp - cfirst, kNb, s);
-                }
-            }
-        }
-        // ---- P2 + P3 on the local rows below the panel
-        const int l0 = first_local_block_after(c, K) * NB;
-        const int mbelow = c->rows_local - l0;
-        if (mbelow > 0) {
-            float* Wb = c->W + (size_t)l0 * ld;
-            for (int j = 0; j < ninner; ++j) {
-                const int kk = k0 + j * kNb, r = j * kNb;
-                launch_lcol(Pn + (size_t)r * ldp + r, ldp, Wb + kk, ld, mbelow,
-                            tc ? c->la_hi + (size_t)l0 * NB : nullptr, tc ? c->la_lo + (size_t)l0 * NB : nullptr, NB, r, s);
-                const int nin = kb - (r + kNb);           // columns of the panel still to the right
-                if (nin > 0) {
-                    int rc = gemm_update(c, Wb + kk, ld, Pn + (size_t)r * ldp + r + kNb, ldp,
-                                         tc ? c->la_hi + (size_t)l0 * NB + r : nullptr, tc ? c->la_lo + (size_t)l0 * NB + r : nullptr,
-                                         tc ? c->ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? c->ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
-                                         Wb + kk + kNb, mbelow, nin, kNb);
-                    if (rc) return rc;
-                }
-            }
-            const int ui = c->upd_count;
-            CK(cudaEventRecord(c->upd_ev[2 * ui], s));
-            int rc = gemm_update(c, Wb + k0, ld, Pn + kb, ldp,
-                                 c->la_hi ? c->la_hi + (size_t)l0 * NB : nullptr, c->la_lo ? c->la_lo + (size_t)l0 * NB : nullptr,
-                                 c->ub_hi ? c->ub_hi + (size_t)(k0 + kb) * NB : nullptr, c->ub_lo ? c->ub_lo + (size_t)(k0 + kb) * NB : nullptr,
-                                 Wb + k0 + kb, mbelow, ld - (k0 + kb), kb);
+    const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
+    const int lrow = blk_local_row(c, K);
+    float* P = c->W + (size_t)lrow * ld;
+    for (int j = 0; j < ninner; ++j) {
+        const int kk = k0 + j * kNb, r = j * kNb;
+        launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
+        launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+                    tc ? ub_hi + (size_t)(kk + kNb) * NB : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB : nullptr, NB, r, s);
+        const int mrem = kb - (r + kNb);
+        if (mrem > 0) {
+            launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
+                        tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB : nullptr, NB, r, s);
+            int rc = gemm_update(c, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                                 tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
+                                 tc ? ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
+                                 P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
             if (rc) return rc;
-            CK(cudaEventRecord(c->upd_ev[2 * ui + 1], s));
-            c->upd_flops[ui] = 2.0 * (double)mbelow * (double)(np + 1 - (k0 + kb)) * (double)kb;
-            c->upd_count = ui + 1;
         }
     }
+    return GAUSS_CUDA_OK;
+}
+
+// Non-owners in 3xTF32 mode: rebuild the split, transposed U operand from the raw broadcast panel.
+static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr)
+{
+    const int NB = c->NB, k0 = K * NB, ninner = blk_rows(c, K) / kNb;
+    for (int j = 0; j < ninner; ++j) {
+        const int r = j * kNb, cfirst = r + kNb;          // panel-relative first column right of inner block j
+        launch_split_transpose(pr.p + (size_t)r * pr.ld + cfirst, pr.ld,
+                               pr.ub_hi + (size_t)(k0 + cfirst) * NB + r, pr.ub_lo + (size_t)(k0 + cfirst) * NB + r,
+                               NB, kNb, c->ld - k0 - cfirst, kNb, c->s_main);
+    }
+}
+
+// P2: L-col solves and in-panel updates for the local rows [row_lo, rows_local).
+static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo)
+{
+    cudaStream_t s = c->s_main;
+    const int ld = c->ld, NB = c->NB;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
+    const int m = c->rows_local - row_lo;
+    if (m <= 0) return GAUSS_CUDA_OK;
+    float* Wb = c->W + (size_t)row_lo * ld;
+    for (int j = 0; j < ninner; ++j) {
+        const int kk = k0 + j * kNb, r = j * kNb;
+        launch_lcol(pr.p + (size_t)r * pr.ld + r, pr.ld, Wb + kk, ld, m,
+                    tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr, NB, r, s);
+        const int nin = kb - (r + kNb);                    // columns of the panel still to the right
+        if (nin > 0) {
+            int rc = gemm_update(c, Wb + kk, ld, pr.p + (size_t)r * pr.ld + r + kNb, pr.ld,
+                                 tc ? c->la_hi + (size_t)row_lo * NB + r : nullptr, tc ? c->la_lo + (size_t)row_lo * NB + r : nullptr,
+                                 tc ? pr.ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? pr.ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
+                                 Wb + kk + kNb, m, nin, kNb);
+            if (rc) return rc;
+        }
+    }
+    return GAUSS_CUDA_OK;
+}
+
+// P3: A22 -= L21 * U12 for the local rows [row_lo, row_hi), all columns right of the panel.  Timed.
+static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo, int row_hi)
+{
+    cudaStream_t s = c->s_main;
+    const int ld = c->ld, NB = c->NB, np = c->np;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    const int k0 = K * NB, kb = blk_rows(c, K);
+    const int m = row_hi - row_lo;
+    if (m <= 0 || ld - (k0 + kb) <= 0) return GAUSS_CUDA_OK;
+    float* Wb = c->W + (size_t)row_lo * ld;
+    const int ui = c->upd_count;
+    const bool timed = (size_t)(2 * ui + 1) < c->upd_ev.size();
+    if (timed) CK(cudaEventRecord(c->upd_ev[2 * ui], s));
+    int rc = gemm_update(c, Wb + k0, ld, pr.p + kb, pr.ld,
+                         tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr,
+                         tc ? pr.ub_hi + (size_t)(k0 + kb) * NB : nullptr, tc ? pr.ub_lo + (size_t)(k0 + kb) * NB : nullptr,
+                         Wb + k0 + kb, m, ld - (k0 + kb), kb);
+    if (rc) return rc;
+    if (timed) {
+        CK(cudaEventRecord(c->upd_ev[2 * ui + 1], s));
+        c->upd_flops[ui] = 2.0 * (double)m * (double)(np + 1 - (k0 + kb)) * (double)kb;
+        c->upd_count = ui + 1;
+    }
+    return GAUSS_CUDA_OK;
+}
+
+// Single GPU: P1 -> P2 -> P3 per outer block, one stream.
+static int factor_single(gauss_cuda_ctx* c)
+{
+    const int ld = c->ld, NB = c->NB;
+    for (int K = 0; K < c->nblk; ++K) {
+        int rc = panel_factor(c, K, c->ub_hi[0], c->ub_lo[0]);
+        if (rc) return rc;
+        PanelRef pr{c->W + (size_t)blk_local_row(c, K) * ld + K * NB, ld, c->ub_hi[0], c->ub_lo[0]};
+        const int l0 = first_local_block_after(c, K) * NB;
+        if ((rc = col_panel(c, K, pr, l0))) return rc;
+        if ((rc = trailing_update(c, K, pr, l0, c->rows_local))) return rc;
+    }
+    return GAUSS_CUDA_OK;
+}
+
+// Multi-GPU with look-ahead.  The owner of block K+1 updates that block's rows first, factors the
+// panel and hands it to the communication stream, so the broadcast (the reference's per-step
+// MPI_Bcast, gauss_mpi :137) and the panel factorisation overlap with everybody's trailing update
+// of step K.  Panel buffers and split U operands are double buffered by the parity of K.
+static int factor_lookahead(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main, sc = c->s_comm;
+    const int ld = c->ld, NB = c->NB;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    auto owner_of = [&](int K) { return K % c->world; };
+    // enqueue on the comm stream: (owner) pack panel K, then broadcast it into pbuf[K&1]
+    auto enqueue_bcast = [&](int K) -> int {
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K), ldp = ld - k0;
+        CK(cudaStreamWaitEvent(sc, c->ev_free[b], 0));            // last readers of pbuf[b] are done
+        if (owner_of(K) == c->rank) {
+            CK(cudaStreamWaitEvent(sc, c->ev_ready[b], 0));       // P1(K) finished on the main stream
+            const float* P = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+            CK(cudaMemcpy2DAsync(c->pbuf[b], (size_t)ldp * sizeof(float), P, (size_t)ld * sizeof(float),
+                                 (size_t)ldp * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
+        }
+        NK(g_nccl.Broadcast(c->pbuf[b], c->pbuf[b], (size_t)kb * ldp, ncclFloat, owner_of(K), c->comm, sc));
+        if (owner_of(K) != c->rank) c->bcast_bytes += (double)kb * ldp * sizeof(float);
+        CK(cudaEventRecord(c->ev_done[b], sc));
+        return GAUSS_CUDA_OK;
+    };
+    int rc;
+    // both panel buffers start out free
+    CK(cudaEventRecord(c->ev_free[0], s));
+    CK(cudaEventRecord(c->ev_free[1], s));
+    if (owner_of(0) == c->rank) {
+        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0]))) return rc;
+        CK(cudaEventRecord(c->ev_ready[0], s));
+    }
+    if ((rc = enqueue_bcast(0))) return rc;
+    for (int K = 0; K < c->nblk; ++K) {
+        const int b = K & 1, k0 = K * NB;
+        const bool mine = owner_of(K) == c->rank;
+        PanelRef pr;
+        if (mine) {                                               // the owner reads its panel in place
+            pr = PanelRef{c->W + (size_t)blk_local_row(c, K) * ld + k0, ld, c->ub_hi[b], c->ub_lo[b]};
+        } else {
+            CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));
+            pr = PanelRef{c->pbuf[b], ld - k0, c->ub_hi[b], c->ub_lo[b]};
+            if (tc) rebuild_split_u(c, K, pr);
+        }
+        const int l0 = first_local_block_after(c, K) * NB;
+        if ((rc = col_panel(c, K, pr, l0))) return rc;
+        int rest_lo = l0;
+        if (K + 1 < c->nblk) {
+            if (owner_of(K + 1) == c->rank) {
+                // block K+1 is this rank's first block below the panel: bring it up to date, factor it
+                const int rows_next = blk_rows(c, K + 1);
+                if ((rc = trailing_update(c, K, pr, l0, l0 + rows_next))) return rc;
+                if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1]))) return rc;
+                CK(cudaEventRecord(c->ev_ready[b ^ 1], s));
+                rest_lo = l0 + rows_next;
+            }
+            if ((rc = enqueue_bcast(K + 1))) return rc;
+        }
+        if ((rc = trailing_update(c, K, pr, rest_lo, c->rows_local))) return rc;
+        CK(cudaEventRecord(c->ev_free[b], s));                    // pbuf[b] / ub[b] may be overwritten from here on
+    }
+    CK(cudaEventRecord(c->ev_done[0], sc));
+    CK(cudaStreamWaitEvent(s, c->ev_done[0], 0));                 // join the comm stream
+    return GAUSS_CUDA_OK;
+}
+
+static int factor(gauss_cuda_ctx* c)
+{
+    CK(cudaMemsetAsync(c->status, 0, sizeof(int), c->s_main));
+    c->bcast_bytes = 0.0;
+    c->upd_count = 0;
+    int rc = c->world > 1 ? factor_lookahead(c) : factor_single(c);
+    if (rc) return rc;
     CK(cudaGetLastError());
     c->factored = true;
     return GAUSS_CUDA_OK;

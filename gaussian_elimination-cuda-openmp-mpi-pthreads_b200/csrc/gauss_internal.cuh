@@ -51,6 +51,7 @@ void launch_split_rowmajor(const float* src, int lds, float* hi, float* lo, int 
 // split_transpose: hi/lo[c*ldd + r] = split(src[r*lds + c]) for c < cols, r < rext (source rows >= rows read as 0).
 void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, int rext, cudaStream_t s);
 void simt_setup_device();     // per-device dynamic shared memory opt-ins of the SIMT kernels
+void panel_setup_device();    // same for lu_panel.cu (called by simt_setup_device)
 int  tc_setup_device();       // same for the tile engine; returns a GAUSS_CUDA_* status
 
 // ---- tensor-core tile engine (tc_gemm.cu) -----------------------------------------------

@@ -22,124 +22,109 @@ __device__ __forceinline__ void tf32_split2(float x, float& hi, float& lo) {
     hi = tf32_round(x);
     lo = tf32_round(x - hi);
 }
-__device__ __forceinline__ void bar_named(int id, int nthreads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+// 16-byte asynchronous global -> shared copy (LDGSTS): all copies of a stage are in flight together, so
+// the global-memory latency is paid once per stage instead of once per loop iteration
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
 }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // =====================================================================================
-// 1. Diagonal block factor
+// 1. Diagonal block factor: 128x128, one CTA of 256 threads, the block lives in registers
+//    (16x16 thread grid, cyclic 8x8 elements per thread).  Latency is everything here, so the
+//    per-pivot chain is kept to  STS -> barrier -> LDS -> rcp -> FMUL -> FFMA :
+//      * row k and column k are published RAW (no normalisation on the chain); every thread forms
+//        the reciprocal of the pivot itself and scales its multipliers (a_ik / a_kk), i.e. the step is
+//        done in Doolittle form and U is scaled to the reference's unit-diagonal form (getPivot
+//        :100-111) once at the end, with the same reciprocals;
+//      * the update is branch-free (masked operands instead of predicated code), the loops over
+//        the 16 pivots of a phase are rolled so the code stays hot in the instruction cache.
 // =====================================================================================
-constexpr int DLD = kNb + 4;      // shared-memory row stride (floats)
+__device__ __forceinline__ float fast_rcp(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return fmaf(r, fmaf(-x, r, 1.0f), r);                 // one Newton step: full FP32 accuracy, exact for powers of two
+}
+
 struct DiagSmem {
-    float S[kNb][DLD];
-    float rowbuf[2][32];
+    float rowbuf[2][kNb];
+    float colbuf[2][kNb];
     float rinv[kNb];
     int first_bad;
 };
 
-template <int B>
-__device__ __forceinline__ void diag_block(DiagSmem& sm, const int tid)
+template <int PH>
+__device__ __forceinline__ void diag_phase(float (&a)[8][8], DiagSmem& sm, const int tx, const int ty)
 {
-    constexpr int o = 32 * B;          // first row/column of this sub-block
-    constexpr int R = kNb - o;         // rows in the column panel
-    constexpr int Cb = R - 32;         // columns right of the panel inside the 128 block
-    // (a) factor the (R x 32) column panel: thread t owns row o+t, 32 entries in registers; one
-    //     named barrier per pivot step, the normalised pivot row travels through rowbuf
-    if (tid < R) {
-        float p[32];
-        const float* src = &sm.S[o + tid][o];
+#pragma unroll 1
+    for (int kk = 0; kk < 16; ++kk) {
+        const int k = PH * 16 + kk;
+        float* rb = sm.rowbuf[k & 1];
+        float* cb = sm.colbuf[k & 1];
+        if (ty == kk) {                                    // holders of row k: raw values, pivot included
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-            const float4 v = *reinterpret_cast<const float4*>(src + j);
-            p[j] = v.x; p[j + 1] = v.y; p[j + 2] = v.z; p[j + 3] = v.w;
+            for (int q = PH; q < 8; ++q) rb[tx + 16 * q] = a[PH][q];
         }
+        if (tx == kk) {                                    // holders of column k: raw multipliers a_ik
 #pragma unroll
-        for (int kk = 0; kk < 32; ++kk) {
-            float* rb = sm.rowbuf[kk & 1];
-            if (tid == kk) {
-                const float piv = p[kk];
-                if (!(fabsf(piv) > 0.f) || isinf(piv)) atomicMin(&sm.first_bad, o + kk);
-                const float r = 1.0f / piv;                    // getPivot :105-107 (reciprocal instead of 31 divisions)
-                sm.rinv[o + kk] = r;
-#pragma unroll
-                for (int j = kk + 1; j < 32; ++j) { p[j] *= r; rb[j] = p[j]; }
-            }
-            bar_named(1, R);
-            if (tid > kk) {
-                const float l = p[kk];
-#pragma unroll
-                for (int j = kk + 1; j < 32; ++j) p[j] = fmaf(-l, rb[j], p[j]);     // computeGauss :132-134
-            }
-        }
-        float* dst = &sm.S[o + tid][o];
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + j) = make_float4(p[j], p[j + 1], p[j + 2], p[j + 3]);
-    }
-    __syncthreads();
-    if (Cb > 0) {
-        // (b) block row of U right of the panel: one thread per column, forward substitution with the 32x32 L
-        if (tid < Cb) {
-            const int c = o + 32 + tid;
-            float x[32];
-#pragma unroll
-            for (int i = 0; i < 32; ++i) x[i] = sm.S[o + i][c];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                x[j] *= sm.rinv[o + j];
-#pragma unroll
-                for (int i = j + 1; i < 32; ++i) x[i] = fmaf(-sm.S[o + i][o + j], x[j], x[i]);
-            }
-#pragma unroll
-            for (int i = 0; i < 32; ++i) sm.S[o + i][c] = x[i];
+            for (int p = PH; p < 8; ++p) cb[ty + 16 * p] = a[p][PH];
         }
         __syncthreads();
-        // (c) rank-32 update of the trailing (Cb x Cb) part, cyclic T x T register tiles
-        constexpr int T = Cb / 16 > 0 ? Cb / 16 : 1;
-        const int ty = tid >> 4, tx = tid & 15;
-        float acc[T][T];
-#pragma unroll
-        for (int i = 0; i < T; ++i)
-#pragma unroll
-            for (int j = 0; j < T; ++j) acc[i][j] = 0.f;
-#pragma unroll 8
-        for (int k = 0; k < 32; ++k) {
-            float a[T], bv[T];
-#pragma unroll
-            for (int i = 0; i < T; ++i) a[i] = sm.S[o + 32 + ty + 16 * i][o + k];
-#pragma unroll
-            for (int j = 0; j < T; ++j) bv[j] = sm.S[o + k][o + 32 + tx + 16 * j];
-#pragma unroll
-            for (int i = 0; i < T; ++i)
-#pragma unroll
-                for (int j = 0; j < T; ++j) acc[i][j] = fmaf(a[i], bv[j], acc[i][j]);
+        const float piv = rb[k];
+        const float r = fast_rcp(piv);
+        if (tx == kk && ty == kk) {
+            sm.rinv[k] = r;
+            if (!(fabsf(piv) > 0.f) || isinf(piv)) atomicMin(&sm.first_bad, k);
         }
+        // only the first row/column group of the phase can still contain indices <= k
+        float rv[8], lv[8];
+        rv[PH] = (tx > kk) ? rb[tx + 16 * PH] : 0.f;
+        lv[PH] = (ty > kk) ? cb[ty + 16 * PH] * r : 0.f;
 #pragma unroll
-        for (int i = 0; i < T; ++i)
+        for (int q = PH + 1; q < 8; ++q) rv[q] = rb[tx + 16 * q];
 #pragma unroll
-            for (int j = 0; j < T; ++j) sm.S[o + 32 + ty + 16 * i][o + 32 + tx + 16 * j] -= acc[i][j];
-        __syncthreads();
+        for (int p = PH + 1; p < 8; ++p) lv[p] = cb[ty + 16 * p] * r;
+#pragma unroll
+        for (int p = PH; p < 8; ++p)
+#pragma unroll
+            for (int q = PH; q < 8; ++q) a[p][q] = fmaf(-lv[p], rv[q], a[p][q]);     // computeGauss :132-134
     }
 }
 
 __global__ void __launch_bounds__(256, 1)
 diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__ status)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    DiagSmem& sm = *reinterpret_cast<DiagSmem*>(smem_raw);
-    const int tid = threadIdx.x;
+    __shared__ DiagSmem sm;
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
     if (tid == 0) sm.first_bad = kNb;
-    for (int idx = tid; idx < kNb * kNb / 4; idx += 256) {
-        const int r = idx >> 5, c4 = (idx & 31) << 2;
-        *reinterpret_cast<float4*>(&sm.S[r][c4]) = *reinterpret_cast<const float4*>(blk + (size_t)r * ld + c4);
-    }
+    float a[8][8];
+#pragma unroll
+    for (int p = 0; p < 8; ++p)
+#pragma unroll
+        for (int q = 0; q < 8; ++q) a[p][q] = blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q];
+    diag_phase<0>(a, sm, tx, ty);
+    diag_phase<1>(a, sm, tx, ty);
+    diag_phase<2>(a, sm, tx, ty);
+    diag_phase<3>(a, sm, tx, ty);
+    diag_phase<4>(a, sm, tx, ty);
+    diag_phase<5>(a, sm, tx, ty);
+    diag_phase<6>(a, sm, tx, ty);
+    diag_phase<7>(a, sm, tx, ty);
     __syncthreads();
-    diag_block<0>(sm, tid);
-    diag_block<1>(sm, tid);
-    diag_block<2>(sm, tid);
-    diag_block<3>(sm, tid);
-    for (int idx = tid; idx < kNb * kNb / 4; idx += 256) {
-        const int r = idx >> 5, c4 = (idx & 31) << 2;
-        *reinterpret_cast<float4*>(blk + (size_t)r * ld + c4) = *reinterpret_cast<const float4*>(&sm.S[r][c4]);
+    // U to unit-diagonal form: row i (above the diagonal) times 1/pivot_i; L keeps the pivots
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const int i = ty + 16 * p;
+        const float ri = sm.rinv[i];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int j = tx + 16 * q;
+            const float v = (j > i) ? a[p][q] * ri : a[p][q];
+            blk[(size_t)i * ld + j] = v;
+        }
     }
     // earliest bad pivot of this block; the first block to report wins (blocks run in pivot order)
     if (tid == 0 && sm.first_bad < kNb) atomicCAS(status, 0, grow0 + sm.first_bad + 1);
@@ -147,12 +132,15 @@ diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__
 
 void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s)
 {
-    diag_factor_kernel<<<1, 256, sizeof(DiagSmem), s>>>(blk, ld, global_row0, status);
+    diag_factor_kernel<<<1, 256, 0, s>>>(blk, ld, global_row0, status);
     ++g_launch_count;
 }
 
 // =====================================================================================
-// 2. U-row panel:  X = L11^-1 * A12, 64 matrix columns per CTA, 256 threads
+// 2. U-row panel:  X = L11^-1 * A12, 64 matrix columns per CTA, 256 threads.
+//    Code is kept compact on purpose (rolled loops, one shared multiply-accumulate body): these
+//    CTAs run each instruction only a few times, so straight-line unrolled code is bound by cold
+//    instruction fetch rather than by arithmetic.
 // =====================================================================================
 constexpr int UW = 64;
 struct UrowSmem {
@@ -161,32 +149,26 @@ struct UrowSmem {
     float strip[kNb][UW];
 };
 
-// rows [row0, row0 + 8*RPW) of the strip  -=  L[rows, 32b..32b+31] * strip[32b..32b+31, :]
-template <int RPW>
-__device__ __forceinline__ void urow_update(UrowSmem& sm, const int b, const int row0, const int warp, const int lane)
+// acc[i][c] += sum_{k<32} A[i][k] * B[k][lane + 32c]   for 4 rows of A (row stride lda) and a 32 x 64 block B
+__device__ __forceinline__ void mac_4x2(float (&acc)[4][2], const float* __restrict__ A, const int lda,
+                                        const float* __restrict__ B, const int lane)
 {
-    float acc[RPW][2];
-#pragma unroll
-    for (int i = 0; i < RPW; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; }
-    const int r0 = row0 + RPW * warp;
-#pragma unroll
+#pragma unroll 2
     for (int k4 = 0; k4 < 32; k4 += 4) {
-        float4 a[RPW];
+        float4 a[4];
 #pragma unroll
-        for (int i = 0; i < RPW; ++i) a[i] = *reinterpret_cast<const float4*>(&sm.L[r0 + i][32 * b + k4]);
+        for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(A + i * lda + k4);
         float bv[4][2];
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) { bv[kk][0] = sm.strip[32 * b + k4 + kk][lane]; bv[kk][1] = sm.strip[32 * b + k4 + kk][lane + 32]; }
+        for (int kk = 0; kk < 4; ++kk) { bv[kk][0] = B[(k4 + kk) * UW + lane]; bv[kk][1] = B[(k4 + kk) * UW + lane + 32]; }
 #pragma unroll
-        for (int i = 0; i < RPW; ++i) {
+        for (int i = 0; i < 4; ++i) {
             acc[i][0] = fmaf(a[i].x, bv[0][0], acc[i][0]); acc[i][1] = fmaf(a[i].x, bv[0][1], acc[i][1]);
             acc[i][0] = fmaf(a[i].y, bv[1][0], acc[i][0]); acc[i][1] = fmaf(a[i].y, bv[1][1], acc[i][1]);
             acc[i][0] = fmaf(a[i].z, bv[2][0], acc[i][0]); acc[i][1] = fmaf(a[i].z, bv[2][1], acc[i][1]);
             acc[i][0] = fmaf(a[i].w, bv[3][0], acc[i][0]); acc[i][1] = fmaf(a[i].w, bv[3][1], acc[i][1]);
         }
     }
-#pragma unroll
-    for (int i = 0; i < RPW; ++i) { sm.strip[r0 + i][lane] -= acc[i][0]; sm.strip[r0 + i][lane + 32] -= acc[i][1]; }
 }
 
 __global__ void __launch_bounds__(256, 2)
@@ -198,23 +180,31 @@ urow_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int c0 = blockIdx.x * UW;
 
+    // stage 0: the four 32x32 diagonal sub-blocks of L11 (needed first, for the inverses)
+    for (int idx = tid; idx < 4 * 32 * 8; idx += 256) {
+        const int bb = idx >> 8, r = 32 * bb + ((idx >> 3) & 31), c4 = 32 * bb + ((idx & 7) << 2);
+        cp_async16(&sm.L[r][c4], l11 + (size_t)r * ldl + c4);
+    }
+    cp_async_commit();
+    // stage 1: the rest of L11 and the 128 x 64 strip (columns beyond ncols are the zero padding of W)
     for (int idx = tid; idx < kNb * kNb / 4; idx += 256) {
         const int r = idx >> 5, c4 = (idx & 31) << 2;
-        *reinterpret_cast<float4*>(&sm.L[r][c4]) = *reinterpret_cast<const float4*>(l11 + (size_t)r * ldl + c4);
+        if ((r >> 5) != (c4 >> 5)) cp_async16(&sm.L[r][c4], l11 + (size_t)r * ldl + c4);
     }
-    // strip: 128 rows x 64 columns, float4 per thread (columns beyond ncols are the zero padding of W)
     {
         const int c4 = (tid & 15) << 2;
         const bool ok = c0 + c4 < ncols;
         for (int r = tid >> 4; r < kNb; r += 16) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ok) v = *reinterpret_cast<const float4*>(a12 + (size_t)r * ld + c0 + c4);
-            *reinterpret_cast<float4*>(&sm.strip[r][c4]) = v;
+            if (ok) cp_async16(&sm.strip[r][c4], a12 + (size_t)r * ld + c0 + c4);
+            else *reinterpret_cast<float4*>(&sm.strip[r][c4]) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
+    cp_async_commit();
+    cp_async_wait<1>();
     __syncthreads();
     if (warp < 4) {
-        // inverse of the 32x32 lower-triangular diagonal sub-block `warp`: lane c solves L x = e_c
+        // inverse of the 32x32 lower-triangular diagonal sub-block `warp`: lane c solves L x = e_c by
+        // forward substitution, the column held in registers (the L entries are warp-wide broadcasts)
         const int o = 32 * warp;
         const float myrinv = 1.0f / sm.L[o + lane][o + lane];
         float x[32];
@@ -229,37 +219,30 @@ urow_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int
 #pragma unroll
         for (int i = 0; i < 32; ++i) sm.invLd[warp][i][lane] = x[i];
     }
+    cp_async_wait<0>();
     __syncthreads();
 
 #pragma unroll 1
     for (int b = 0; b < 4; ++b) {
+        const float* Bb = &sm.strip[32 * b][0];
         // X_b = inv(L_bb) * strip_b : warp w -> rows 4w..4w+3 of the sub-block, lane -> columns lane, lane+32
         float acc[4][2];
 #pragma unroll
         for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; }
-#pragma unroll
-        for (int k4 = 0; k4 < 32; k4 += 4) {
-            float4 a[4];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(&sm.invLd[b][4 * warp + i][k4]);
-            float bv[4][2];
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk) { bv[kk][0] = sm.strip[32 * b + k4 + kk][lane]; bv[kk][1] = sm.strip[32 * b + k4 + kk][lane + 32]; }
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                acc[i][0] = fmaf(a[i].x, bv[0][0], acc[i][0]); acc[i][1] = fmaf(a[i].x, bv[0][1], acc[i][1]);
-                acc[i][0] = fmaf(a[i].y, bv[1][0], acc[i][0]); acc[i][1] = fmaf(a[i].y, bv[1][1], acc[i][1]);
-                acc[i][0] = fmaf(a[i].z, bv[2][0], acc[i][0]); acc[i][1] = fmaf(a[i].z, bv[2][1], acc[i][1]);
-                acc[i][0] = fmaf(a[i].w, bv[3][0], acc[i][0]); acc[i][1] = fmaf(a[i].w, bv[3][1], acc[i][1]);
-            }
-        }
+        mac_4x2(acc, &sm.invLd[b][4 * warp][0], 32, Bb, lane);
         __syncthreads();                                   // every read of strip_b is done
 #pragma unroll
         for (int i = 0; i < 4; ++i) { sm.strip[32 * b + 4 * warp + i][lane] = acc[i][0]; sm.strip[32 * b + 4 * warp + i][lane + 32] = acc[i][1]; }
         __syncthreads();
-        if (b == 0)      urow_update<12>(sm, 0, 32, warp, lane);
-        else if (b == 1) urow_update<8>(sm, 1, 64, warp, lane);
-        else if (b == 2) urow_update<4>(sm, 2, 96, warp, lane);
+        // rows below: strip[r] -= L[r, 32b..32b+31] * X_b, 32 rows per pass (4 per warp)
+#pragma unroll 1
+        for (int r0 = 32 * (b + 1) + 4 * warp; r0 < kNb; r0 += 32) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; }
+            mac_4x2(acc, &sm.L[r0][32 * b], kNb, Bb, lane);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { sm.strip[r0 + i][lane] -= acc[i][0]; sm.strip[r0 + i][lane + 32] -= acc[i][1]; }
+        }
         __syncthreads();
     }
 
@@ -275,7 +258,7 @@ urow_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int
         if (c0 + c < ncols) {
             float* dh = ub_hi + (size_t)(c0 + c) * ldub + k_ub + 32 * part;
             float* dl = ub_lo + (size_t)(c0 + c) * ldub + k_ub + 32 * part;
-#pragma unroll
+#pragma unroll 2
             for (int r = 0; r < 32; r += 4) {
                 float4 h, l;
                 tf32_split2(sm.strip[32 * part + r][c], h.x, l.x);
@@ -307,40 +290,22 @@ struct LcolSmem {
     float tile[LH][kNb];
 };
 
-// tile[:, 32(b+1) ...] -= tile[:, 32b..32b+31] * U[32b..32b+31, 32(b+1) ...]   (NJ 32-column groups)
-template <int NJ>
-__device__ __forceinline__ void lcol_update(LcolSmem& sm, const int b, const int warp, const int lane)
+// acc[i] += sum_{k<32} T[i][k] * B[k * ldb + lane]   for 8 rows of the tile (row stride kNb)
+__device__ __forceinline__ void mac_8x1(float (&acc)[8], const float* __restrict__ T, const float* __restrict__ B,
+                                        const int ldb, const int lane)
 {
-    float acc[8][NJ];
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) acc[i][j] = 0.f;
-    const int r0 = 8 * warp, cbase = 32 * (b + 1) + lane;
-#pragma unroll
+#pragma unroll 2
     for (int k4 = 0; k4 < 32; k4 += 4) {
-        float4 a[8];
+        float bv[4];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const float4*>(&sm.tile[r0 + i][32 * b + k4]);
-        float bv[4][NJ];
+        for (int kk = 0; kk < 4; ++kk) bv[kk] = B[(k4 + kk) * ldb + lane];
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-#pragma unroll
-            for (int j = 0; j < NJ; ++j) bv[kk][j] = sm.U[32 * b + k4 + kk][cbase + 32 * j];
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-#pragma unroll
-            for (int j = 0; j < NJ; ++j) {
-                acc[i][j] = fmaf(a[i].x, bv[0][j], acc[i][j]);
-                acc[i][j] = fmaf(a[i].y, bv[1][j], acc[i][j]);
-                acc[i][j] = fmaf(a[i].z, bv[2][j], acc[i][j]);
-                acc[i][j] = fmaf(a[i].w, bv[3][j], acc[i][j]);
-            }
+        for (int i = 0; i < 8; ++i) {
+            const float4 a = *reinterpret_cast<const float4*>(T + i * kNb + k4);
+            acc[i] = fmaf(a.x, bv[0], acc[i]); acc[i] = fmaf(a.y, bv[1], acc[i]);
+            acc[i] = fmaf(a.z, bv[2], acc[i]); acc[i] = fmaf(a.w, bv[3], acc[i]);
+        }
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-        for (int j = 0; j < NJ; ++j) sm.tile[r0 + i][cbase + 32 * j] -= acc[i][j];
 }
 
 __global__ void __launch_bounds__(256, 2)
@@ -352,18 +317,27 @@ lcol_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int row0 = blockIdx.x * LH;
 
+    // stage 0: the four 32x32 diagonal sub-blocks of U11 (needed first, for the inverses)
+    for (int idx = tid; idx < 4 * 32 * 8; idx += 256) {
+        const int bb = idx >> 8, r = 32 * bb + ((idx >> 3) & 31), c4 = 32 * bb + ((idx & 7) << 2);
+        cp_async16(&sm.U[r][c4], u11 + (size_t)r * ldu + c4);
+    }
+    cp_async_commit();
+    // stage 1: the rest of U11 and the 64 x 128 tile of rows
     for (int idx = tid; idx < kNb * kNb / 4; idx += 256) {
         const int r = idx >> 5, c4 = (idx & 31) << 2;
-        *reinterpret_cast<float4*>(&sm.U[r][c4]) = *reinterpret_cast<const float4*>(u11 + (size_t)r * ldu + c4);
+        if ((r >> 5) != (c4 >> 5)) cp_async16(&sm.U[r][c4], u11 + (size_t)r * ldu + c4);
     }
     for (int r = warp; r < LH; r += 8) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row0 + r < nrows) v = *reinterpret_cast<const float4*>(a21 + (size_t)(row0 + r) * ld + 4 * lane);
-        *reinterpret_cast<float4*>(&sm.tile[r][4 * lane]) = v;
+        if (row0 + r < nrows) cp_async16(&sm.tile[r][4 * lane], a21 + (size_t)(row0 + r) * ld + 4 * lane);
+        else *reinterpret_cast<float4*>(&sm.tile[r][4 * lane]) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
+    cp_async_commit();
+    cp_async_wait<1>();
     __syncthreads();
     if (warp < 4) {
-        // inverse of the 32x32 unit-upper diagonal sub-block `warp`: lane c solves U x = e_c from the bottom up
+        // inverse of the 32x32 unit-upper diagonal sub-block `warp`: lane c solves U x = e_c from the
+        // bottom up, the column held in registers
         const int o = 32 * warp;
         float x[32];
 #pragma unroll
@@ -376,33 +350,30 @@ lcol_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int
 #pragma unroll
         for (int i = 0; i < 32; ++i) sm.invUd[warp][i][lane] = x[i];
     }
+    cp_async_wait<0>();
     __syncthreads();
 
+    float* T = &sm.tile[8 * warp][0];                      // a warp only ever touches its own 8 rows of the tile
 #pragma unroll 1
     for (int b = 0; b < 4; ++b) {
-        // X_b = tile_b * inv(U_bb) : warp w -> rows 8w..8w+7, lane -> column lane of the sub-block
+        // X_b = tile_b * inv(U_bb) : lane -> column lane of the sub-block
         float acc[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-#pragma unroll
-        for (int k4 = 0; k4 < 32; k4 += 4) {
-            float bv[4];
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk) bv[kk] = sm.invUd[b][k4 + kk][lane];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const float4 a = *reinterpret_cast<const float4*>(&sm.tile[8 * warp + i][32 * b + k4]);
-                acc[i] = fmaf(a.x, bv[0], acc[i]); acc[i] = fmaf(a.y, bv[1], acc[i]);
-                acc[i] = fmaf(a.z, bv[2], acc[i]); acc[i] = fmaf(a.w, bv[3], acc[i]);
-            }
-        }
-        __syncwarp();                                       // a warp only reads/writes its own 8 rows of tile_b
-#pragma unroll
-        for (int i = 0; i < 8; ++i) sm.tile[8 * warp + i][32 * b + lane] = acc[i];
+        mac_8x1(acc, T + 32 * b, &sm.invUd[b][0][0], 32, lane);
         __syncwarp();
-        if (b == 0)      lcol_update<3>(sm, 0, warp, lane);
-        else if (b == 1) lcol_update<2>(sm, 1, warp, lane);
-        else if (b == 2) lcol_update<1>(sm, 2, warp, lane);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) T[i * kNb + 32 * b + lane] = acc[i];
+        __syncwarp();
+        // columns right: tile[:, 32(b+1)+ ...] -= X_b * U[32b..32b+31, those columns], 32 columns per pass
+#pragma unroll 1
+        for (int cb = 32 * (b + 1); cb < kNb; cb += 32) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+            mac_8x1(acc, T + 32 * b, &sm.U[32 * b][cb], kNb, lane);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) T[i * kNb + cb + lane] -= acc[i];
+        }
         __syncwarp();
     }
     __syncthreads();
@@ -430,7 +401,6 @@ void launch_lcol(const float* u11, int ldu, float* a21, int ld, int nrows,
 
 void panel_setup_device()
 {
-    cudaFuncSetAttribute(diag_factor_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(DiagSmem));
     cudaFuncSetAttribute(urow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowSmem));
     cudaFuncSetAttribute(lcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolSmem));
 }

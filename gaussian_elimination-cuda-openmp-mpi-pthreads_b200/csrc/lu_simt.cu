@@ -1,6 +1,6 @@
-// SIMT (FP32 FFMA) kernels of the blocked no-pivot LU: the latency-critical diagonal-block
-// factor, the two triangular panel solves, the FFMA GEMM used by GAUSS_CUDA_MODE_FFMA, the
-// blocked back substitution and a few layout helpers.  sm_100a only.
+// SIMT (FP32 FFMA) kernels of the blocked no-pivot LU: the FFMA GEMM used by GAUSS_CUDA_MODE_FFMA,
+// the blocked back substitution and a few layout helpers (the panel kernels are in lu_panel.cu).
+// sm_100a only.
 //
 // Reference semantics being reproduced (OpenMP_and_MPI/gauss_openmp/gauss_internal_input.c):
 //   getPivot  :100-111  row i is divided by its pivot (true division), diagonal becomes 1
@@ -24,281 +24,7 @@ __device__ __forceinline__ void tf32_split(float x, float& hi, float& lo) {
     lo = tf32_hi(x - hi);
 }
 
-// =====================================================================================
-// 1. Diagonal block factor: 128x128, one CTA of 256 threads, the block lives in registers
-//    (16x16 thread grid, cyclic 8x8 elements per thread); per pivot step the normalised
-//    pivot row and the multiplier column are exchanged through double-buffered shared
-//    memory (one __syncthreads per step), the pivot itself by a warp shuffle.
-// =====================================================================================
-template <int PH>
-__device__ __forceinline__ void diag_phase(float (&a)[8][8], float (&rowbuf)[2][kNb], float (&colbuf)[2][kNb],
-                                           const int tx, const int ty, const int warp, int& bad)
-{
-#pragma unroll 1
-    for (int kk = 0; kk < 16; ++kk) {
-        const int k = PH * 16 + kk;
-        float* rb = rowbuf[k & 1];
-        float* cb = colbuf[k & 1];
-        if (warp == (kk >> 1)) {                      // the warp holding row k (warp-uniform branch)
-            const float piv = __shfl_sync(0xffffffffu, a[PH][PH], ((kk & 1) << 4) | kk);
-            if (ty == kk) {
-                if (tx == kk && (!(fabsf(piv) > 0.f) || isinf(piv)) && bad < 0) bad = k;
-#pragma unroll
-                for (int q = PH; q < 8; ++q) {
-                    const int j = tx + 16 * q;
-                    if (j > k) {
-                        a[PH][q] = __fdiv_rn(a[PH][q], piv);     // getPivot :105-107
-                        rb[j] = a[PH][q];
-                    }
-                }
-            }
-        }
-        if (tx == kk) {
-#pragma unroll
-            for (int p = PH; p < 8; ++p) {
-                const int i = ty + 16 * p;
-                if (i > k) cb[i] = a[p][PH];
-            }
-        }
-        __syncthreads();
-        float rv[8];
-#pragma unroll
-        for (int q = PH; q < 8; ++q) rv[q] = rb[tx + 16 * q];
-#pragma unroll
-        for (int p = PH; p < 8; ++p) {
-            const int i = ty + 16 * p;
-            if (i > k) {
-                const float l = cb[i];
-#pragma unroll
-                for (int q = PH; q < 8; ++q)
-                    if (tx + 16 * q > k) a[p][q] = fmaf(-l, rv[q], a[p][q]);   // computeGauss :132-134
-            }
-        }
-    }
-}
-
-__global__ void __launch_bounds__(256, 1)
-diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__ status)
-{
-    __shared__ float rowbuf[2][kNb];
-    __shared__ float colbuf[2][kNb];
-    __shared__ int first_bad;
-    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, warp = tid >> 5;
-    if (tid == 0) first_bad = kNb;
-    float a[8][8];
-#pragma unroll
-    for (int p = 0; p < 8; ++p)
-#pragma unroll
-        for (int q = 0; q < 8; ++q) a[p][q] = blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q];
-    int bad = -1;
-    diag_phase<0>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<1>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<2>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<3>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<4>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<5>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<6>(a, rowbuf, colbuf, tx, ty, warp, bad);
-    diag_phase<7>(a, rowbuf, colbuf, tx, ty, warp, bad);
-#pragma unroll
-    for (int p = 0; p < 8; ++p)
-#pragma unroll
-        for (int q = 0; q < 8; ++q) blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q] = a[p][q];
-    // earliest bad pivot of this block; the first block to report wins (blocks run in pivot order)
-    if (bad >= 0) atomicMin(&first_bad, bad);
-    __syncthreads();
-    if (tid == 0 && first_bad < kNb) atomicCAS(status, 0, grow0 + first_bad + 1);
-}
-
-void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s)
-{
-    diag_factor_kernel<<<1, 256, 0, s>>>(blk, ld, global_row0, status);
-    ++g_launch_count;
-}
-
-// =====================================================================================
-// 2. U-row panel: X = L11^-1 * A12.  One thread per matrix column, 64 columns per CTA,
-//    the 128-row strip in shared memory; 32-row sub-blocks: an unrolled in-register
-//    triangular solve, then a rank-32 update of the rows below.
-// =====================================================================================
-constexpr int kStripW = 64;
-struct UrowSmem {
-    float L[kNb][kNb];            // row-major L11 (only i >= j read)
-    float Ld[4][32][32];          // Ld[b][j][i] = L[32b+i][32b+j]  (transposed diagonal sub-blocks)
-    float strip[kNb][kStripW];
-};
-
-__global__ void __launch_bounds__(kStripW)
-urow_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int ld, int ncols,
-            float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
-{
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    UrowSmem& sm = *reinterpret_cast<UrowSmem*>(smem_raw);
-    const int tx = threadIdx.x;
-    const int c = blockIdx.x * kStripW + tx;
-    const bool live = c < ncols;
-
-    // L11 -> smem, float4, coalesced
-    for (int idx = tx; idx < kNb * kNb / 4; idx += kStripW) {
-        const int r = idx >> 5, c4 = (idx & 31) << 2;
-        const float4 v = *reinterpret_cast<const float4*>(l11 + (size_t)r * ldl + c4);
-        *reinterpret_cast<float4*>(&sm.L[r][c4]) = v;
-    }
-    for (int r = 0; r < kNb; ++r) sm.strip[r][tx] = live ? a12[(size_t)r * ld + c] : 0.f;
-    __syncthreads();
-    for (int idx = tx; idx < 4 * 32 * 32; idx += kStripW) {
-        const int b = idx >> 10, j = (idx >> 5) & 31, i = idx & 31;
-        sm.Ld[b][j][i] = sm.L[32 * b + i][32 * b + j];
-    }
-    __syncthreads();
-
-#pragma unroll 1
-    for (int b = 0; b < 4; ++b) {
-        float x[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) x[i] = sm.strip[32 * b + i][tx];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            x[j] = __fdiv_rn(x[j], sm.Ld[b][j][j]);               // getPivot :105-107 (division by the pivot)
-#pragma unroll
-            for (int i = j + 1; i < 32; ++i) x[i] = fmaf(-sm.Ld[b][j][i], x[j], x[i]);
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) sm.strip[32 * b + i][tx] = x[i];
-        // rows below this sub-block: strip[r] -= L[r][32b .. 32b+31] . x
-#pragma unroll 1
-        for (int r = 32 * (b + 1); r < kNb; r += 4) {
-            float acc0 = sm.strip[r][tx], acc1 = sm.strip[r + 1][tx], acc2 = sm.strip[r + 2][tx], acc3 = sm.strip[r + 3][tx];
-#pragma unroll
-            for (int j4 = 0; j4 < 32; j4 += 4) {
-                const float4 l0 = *reinterpret_cast<const float4*>(&sm.L[r][32 * b + j4]);
-                const float4 l1 = *reinterpret_cast<const float4*>(&sm.L[r + 1][32 * b + j4]);
-                const float4 l2 = *reinterpret_cast<const float4*>(&sm.L[r + 2][32 * b + j4]);
-                const float4 l3 = *reinterpret_cast<const float4*>(&sm.L[r + 3][32 * b + j4]);
-                acc0 = fmaf(-l0.x, x[j4], acc0); acc0 = fmaf(-l0.y, x[j4 + 1], acc0); acc0 = fmaf(-l0.z, x[j4 + 2], acc0); acc0 = fmaf(-l0.w, x[j4 + 3], acc0);
-                acc1 = fmaf(-l1.x, x[j4], acc1); acc1 = fmaf(-l1.y, x[j4 + 1], acc1); acc1 = fmaf(-l1.z, x[j4 + 2], acc1); acc1 = fmaf(-l1.w, x[j4 + 3], acc1);
-                acc2 = fmaf(-l2.x, x[j4], acc2); acc2 = fmaf(-l2.y, x[j4 + 1], acc2); acc2 = fmaf(-l2.z, x[j4 + 2], acc2); acc2 = fmaf(-l2.w, x[j4 + 3], acc2);
-                acc3 = fmaf(-l3.x, x[j4], acc3); acc3 = fmaf(-l3.y, x[j4 + 1], acc3); acc3 = fmaf(-l3.z, x[j4 + 2], acc3); acc3 = fmaf(-l3.w, x[j4 + 3], acc3);
-            }
-            sm.strip[r][tx] = acc0; sm.strip[r + 1][tx] = acc1; sm.strip[r + 2][tx] = acc2; sm.strip[r + 3][tx] = acc3;
-        }
-    }
-    if (!live) return;
-    for (int r = 0; r < kNb; ++r) a12[(size_t)r * ld + c] = sm.strip[r][tx];
-    if (ub_hi != nullptr) {
-        float* dh = ub_hi + (size_t)c * ldub + k_ub;
-        float* dl = ub_lo + (size_t)c * ldub + k_ub;
-        for (int r = 0; r < kNb; r += 4) {
-            float4 h, l;
-            tf32_split(sm.strip[r][tx], h.x, l.x);
-            tf32_split(sm.strip[r + 1][tx], h.y, l.y);
-            tf32_split(sm.strip[r + 2][tx], h.z, l.z);
-            tf32_split(sm.strip[r + 3][tx], h.w, l.w);
-            *reinterpret_cast<float4*>(dh + r) = h;
-            *reinterpret_cast<float4*>(dl + r) = l;
-        }
-    }
-}
-
-void launch_urow(const float* l11, int ldl, float* a12, int ld, int ncols,
-                 float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s)
-{
-    if (ncols <= 0) return;
-    urow_kernel<<<(ncols + kStripW - 1) / kStripW, kStripW, sizeof(UrowSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
-    ++g_launch_count;
-}
-
-// =====================================================================================
-// 3. L-col panel: X = A21 * U11^-1 (U11 unit upper).  One thread per matrix row, 64 rows
-//    per CTA; mirror image of the U-row kernel.
-// =====================================================================================
-constexpr int kTileH = 64;
-constexpr int kUtLd = kNb + 4;
-struct LcolSmem {
-    float Ut[kNb][kUtLd];         // Ut[j][i] = U[i][j]
-    float Ud[4][32][32];          // Ud[b][i][j] = U[32b+i][32b+j]
-    float tile[kTileH][kNb + 1];
-};
-
-__global__ void __launch_bounds__(kTileH)
-lcol_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int ld, int nrows,
-            float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
-{
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    LcolSmem& sm = *reinterpret_cast<LcolSmem*>(smem_raw);
-    const int tx = threadIdx.x;
-    const int row0 = blockIdx.x * kTileH;
-    const int lane = tx & 31, wrp = tx >> 5;
-
-    // U11 -> Ut (transposed) and Ud; coalesced global reads (a warp reads 32 consecutive j of one row i)
-    for (int i = wrp; i < kNb; i += kTileH / 32) {
-#pragma unroll
-        for (int jj = 0; jj < kNb; jj += 32) {
-            const int j = jj + lane;
-            const float v = u11[(size_t)i * ldu + j];
-            sm.Ut[j][i] = v;
-            if ((i >> 5) == (j >> 5)) sm.Ud[i >> 5][i & 31][j & 31] = v;
-        }
-    }
-    // tile rows -> smem (a warp reads one row's 128 floats as float4)
-    for (int r = wrp; r < kTileH; r += kTileH / 32) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row0 + r < nrows) v = *reinterpret_cast<const float4*>(a21 + (size_t)(row0 + r) * ld + 4 * lane);
-        sm.tile[r][4 * lane] = v.x; sm.tile[r][4 * lane + 1] = v.y; sm.tile[r][4 * lane + 2] = v.z; sm.tile[r][4 * lane + 3] = v.w;
-    }
-    __syncthreads();
-
-    float* my = sm.tile[tx];
-#pragma unroll 1
-    for (int b = 0; b < 4; ++b) {
-        float x[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) x[i] = my[32 * b + i];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-#pragma unroll
-            for (int j = i + 1; j < 32; ++j) x[j] = fmaf(-x[i], sm.Ud[b][i][j], x[j]);   // computeGauss :132-134, row-wise
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) my[32 * b + i] = x[i];
-#pragma unroll 1
-        for (int j = 32 * (b + 1); j < kNb; j += 4) {
-            float acc0 = my[j], acc1 = my[j + 1], acc2 = my[j + 2], acc3 = my[j + 3];
-#pragma unroll
-            for (int i4 = 0; i4 < 32; i4 += 4) {
-                const float4 u0 = *reinterpret_cast<const float4*>(&sm.Ut[j][32 * b + i4]);
-                const float4 u1 = *reinterpret_cast<const float4*>(&sm.Ut[j + 1][32 * b + i4]);
-                const float4 u2 = *reinterpret_cast<const float4*>(&sm.Ut[j + 2][32 * b + i4]);
-                const float4 u3 = *reinterpret_cast<const float4*>(&sm.Ut[j + 3][32 * b + i4]);
-                acc0 = fmaf(-u0.x, x[i4], acc0); acc0 = fmaf(-u0.y, x[i4 + 1], acc0); acc0 = fmaf(-u0.z, x[i4 + 2], acc0); acc0 = fmaf(-u0.w, x[i4 + 3], acc0);
-                acc1 = fmaf(-u1.x, x[i4], acc1); acc1 = fmaf(-u1.y, x[i4 + 1], acc1); acc1 = fmaf(-u1.z, x[i4 + 2], acc1); acc1 = fmaf(-u1.w, x[i4 + 3], acc1);
-                acc2 = fmaf(-u2.x, x[i4], acc2); acc2 = fmaf(-u2.y, x[i4 + 1], acc2); acc2 = fmaf(-u2.z, x[i4 + 2], acc2); acc2 = fmaf(-u2.w, x[i4 + 3], acc2);
-                acc3 = fmaf(-u3.x, x[i4], acc3); acc3 = fmaf(-u3.y, x[i4 + 1], acc3); acc3 = fmaf(-u3.z, x[i4 + 2], acc3); acc3 = fmaf(-u3.w, x[i4 + 3], acc3);
-            }
-            my[j] = acc0; my[j + 1] = acc1; my[j + 2] = acc2; my[j + 3] = acc3;
-        }
-    }
-    __syncthreads();
-    // write back: in place, plus the TF32 hi/lo split (A-role operand of the trailing update)
-    for (int r = wrp; r < kTileH; r += kTileH / 32) {
-        if (row0 + r >= nrows) break;
-        float4 v = make_float4(sm.tile[r][4 * lane], sm.tile[r][4 * lane + 1], sm.tile[r][4 * lane + 2], sm.tile[r][4 * lane + 3]);
-        *reinterpret_cast<float4*>(a21 + (size_t)(row0 + r) * ld + 4 * lane) = v;
-        if (la_hi != nullptr) {
-            float4 h, l;
-            tf32_split(v.x, h.x, l.x); tf32_split(v.y, h.y, l.y); tf32_split(v.z, h.z, l.z); tf32_split(v.w, h.w, l.w);
-            *reinterpret_cast<float4*>(la_hi + (size_t)(row0 + r) * ldla + k_la + 4 * lane) = h;
-            *reinterpret_cast<float4*>(la_lo + (size_t)(row0 + r) * ldla + k_la + 4 * lane) = l;
-        }
-    }
-}
-
-void launch_lcol(const float* u11, int ldu, float* a21, int ld, int nrows,
-                 float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s)
-{
-    if (nrows <= 0) return;
-    lcol_kernel<<<(nrows + kTileH - 1) / kTileH, kTileH, sizeof(LcolSmem), s>>>(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
-    ++g_launch_count;
-}
+// (1-3: the diagonal-block factor and the two panel solves live in lu_panel.cu)
 
 // =====================================================================================
 // 4. FP32 FFMA GEMM, NN, row-major: the pure-FFMA variant of the trailing update
@@ -586,8 +312,7 @@ void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int
 // Dynamic shared-memory opt-ins are per device: call once per context with that device current.
 void simt_setup_device()
 {
-    cudaFuncSetAttribute(urow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowSmem));
-    cudaFuncSetAttribute(lcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolSmem));
+    panel_setup_device();
     cudaFuncSetAttribute(trsv_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvDiagSmem);
 }
 
