@@ -136,6 +136,7 @@ struct gauss_cuda_ctx {
     float* xvec = nullptr;   // [np] solution
     float* hvec = nullptr;   // [np] staging for RHS upload / B_out
     int* status = nullptr;   // device: 0 or (row+1) of the first bad pivot
+    int* trsv_ctrl = nullptr;   // device: ticket + per-128-block flags of the fused back substitution
     cudaStream_t s_main = nullptr, s_comm = nullptr;
     cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -199,6 +200,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     A((void**)&c->xvec, (size_t)c->np * sizeof(float));
     A((void**)&c->hvec, (size_t)c->np * sizeof(float));
     A((void**)&c->status, sizeof(int));
+    A((void**)&c->trsv_ctrl, (size_t)(c->np / kNb + 1) * sizeof(int));
     if (world > 1) for (int i = 0; i < 2; ++i) A((void**)&c->pbuf[i], (size_t)c->NB * c->ld * sizeof(float));
     if (mode == GAUSS_CUDA_MODE_3XTF32) {
         const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
@@ -265,6 +267,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi, c->la_lo, c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
     if (c->status) cudaFree(c->status);
+    if (c->trsv_ctrl) cudaFree(c->trsv_ctrl);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->upd_ev) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
@@ -519,6 +522,11 @@ static int backsub(gauss_cuda_ctx* c)
 {
     cudaStream_t s = c->s_main;
     const int ld = c->ld, NB = c->NB, np = c->np;
+    if (c->world == 1) {                   // one launch; U is streamed once, W stays untouched
+        launch_trsv_fused(c->W, ld, np, c->xvec, c->trsv_ctrl, s);
+        CK(cudaGetLastError());
+        return GAUSS_CUDA_OK;
+    }
     for (int K = c->nblk - 1; K >= 0; --K) {
         const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
         const int ninner = kb / kNb;

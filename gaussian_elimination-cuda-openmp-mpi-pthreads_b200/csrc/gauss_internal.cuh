@@ -39,6 +39,9 @@ void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C,
 //              column `ycol` of the same rows (ycol relative to ukk), x also written back there.
 //  trsv_gemv:  y[r] -= U[r, blk] . x  for `nrows` rows starting at `u` (ld), y at column offset ycol.
 void launch_trsv_diag(float* ukk, int ld, int ycol, float* x, cudaStream_t s);
+// Whole back substitution of an [np x ld] factored system in one launch: x = U^-1 * W[:, np].
+// ctrl: np/128 + 1 ints of device scratch (ticket + per-block flags), reset here.  W is not modified.
+void launch_trsv_fused(const float* W, int ld, int np, float* x, int* ctrl, cudaStream_t s);
 void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cudaStream_t s);
 
 // Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.

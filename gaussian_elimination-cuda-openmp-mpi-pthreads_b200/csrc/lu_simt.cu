@@ -9,6 +9,7 @@
 // i.e. Crout LU: A = L*U, U unit upper, L carries the pivots; the RHS is carried as an extra
 // matrix column so `b_j -= m*b_i` (:135) needs no code of its own.
 #include "gauss_internal.cuh"
+#include <stdio.h>
 
 namespace gb200 {
 
@@ -212,6 +213,147 @@ void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cud
 }
 
 // =====================================================================================
+// 5b. Back substitution in ONE launch (single-GPU path).  CTAs take 128-row blocks bottom-up through
+//     an atomic ticket (so a CTA only ever waits for CTAs that already run), stream their rows of U
+//     with float4 loads while folding in x_J as the blocks below publish it (per-block flags,
+//     release/acquire), then solve their own diagonal block with the inverses of its four 32x32
+//     sub-blocks and publish x_r.  U is read exactly once (2*N^2 bytes in total); the dependent chain
+//     per block is: flag -> one 128x128 block product -> 4 small matvecs -> flag.
+// =====================================================================================
+constexpr int TFL = kNb + 4;                 // smem row stride of the diagonal block
+struct TrsvSmem {
+    float U[kNb][TFL];                       // this CTA's diagonal block
+    float invT[4][32][33];                   // invT[b][k][i] = (U_bb^-1)[i][k]
+    float v[kNb];                            // running right-hand side of the block, finally x
+    float red[kNb];
+    int ticket;
+};
+
+__device__ __forceinline__ int ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v) {
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(256, 1)
+trsv_fused_kernel(const float* __restrict__ W, int ld, int np, float* __restrict__ x, int* __restrict__ ctrl)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    TrsvSmem& sm = *reinterpret_cast<TrsvSmem*>(smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nblk = np / kNb;
+    if (tid == 0) sm.ticket = atomicAdd(&ctrl[0], 1);
+    __syncthreads();
+    const int r = nblk - 1 - sm.ticket;      // my row block; every block J > r belongs to an earlier ticket
+    int* flags = ctrl + 1;
+    const float* Wr = W + (size_t)r * kNb * ld;
+
+    // own diagonal block -> smem, its RHS entries -> v
+    for (int idx = tid; idx < kNb * kNb / 4; idx += 256) {
+        const int rr = idx >> 5, c4 = (idx & 31) << 2;
+        *reinterpret_cast<float4*>(&sm.U[rr][c4]) = __ldg(reinterpret_cast<const float4*>(Wr + (size_t)rr * ld + r * kNb + c4));
+    }
+    if (tid < kNb) sm.v[tid] = Wr[(size_t)tid * ld + np];
+
+    // rows 16*warp .. 16*warp+15 of the block; per-lane partial dot products over the lane's 4 columns
+    float part[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) part[i] = 0.f;
+    const float* rowbase = Wr + (size_t)(16 * warp) * ld + 4 * lane;
+    float4 cur[16];
+    int J = nblk - 1;
+    if (J > r) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) cur[i] = __ldcs(reinterpret_cast<const float4*>(rowbase + (size_t)i * ld + J * kNb));
+    }
+    __syncthreads();
+    if (warp < 4) {
+        // inverse of the 32x32 unit-upper diagonal sub-block `warp` (lane c: column c, bottom-up substitution)
+        const int o = 32 * warp;
+        float xi[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) xi[i] = (i == lane) ? 1.f : 0.f;
+#pragma unroll
+        for (int j = 31; j > 0; --j) {
+#pragma unroll
+            for (int i = 0; i < j; ++i) xi[i] = fmaf(-sm.U[o + i][o + j], xi[j], xi[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sm.invT[warp][lane][i] = xi[i];
+    }
+
+    for (; J > r; --J) {
+        float4 nxt[16];
+        if (J - 1 > r) {                      // prefetch the next block of U before waiting for x_J
+#pragma unroll
+            for (int i = 0; i < 16; ++i) nxt[i] = __ldcs(reinterpret_cast<const float4*>(rowbase + (size_t)i * ld + (J - 1) * kNb));
+        }
+        if (lane == 0) {                      // bounded wait: a protocol bug must trap, never hang the GPU
+            const long long t0 = clock64();
+            while (ld_acquire(flags + J) == 0) {
+                __nanosleep(64);
+                if (clock64() - t0 > 4000000000LL) { printf("trsv_fused: wait for block %d timed out (block %d)\n", J, r); __trap(); }
+            }
+        }
+        __syncwarp();
+        const float4 xv = __ldcg(reinterpret_cast<const float4*>(x + J * kNb + 4 * lane));
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            part[i] = fmaf(cur[i].x, xv.x, part[i]); part[i] = fmaf(cur[i].y, xv.y, part[i]);
+            part[i] = fmaf(cur[i].z, xv.z, part[i]); part[i] = fmaf(cur[i].w, xv.w, part[i]);
+        }
+        if (J - 1 > r) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) cur[i] = nxt[i];
+        }
+    }
+    // fold the per-lane partial sums: v[row] -= sum over lanes
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+        float s_ = part[i];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) s_ += __shfl_xor_sync(0xffffffffu, s_, off);
+        if (lane == 0) sm.red[16 * warp + i] = s_;
+    }
+    __syncthreads();
+    if (tid < kNb) sm.v[tid] -= sm.red[tid];
+    __syncthreads();
+    // diagonal block: x_b = inv(U_bb) * v_b, then v_c -= U_cb * x_b for the sub-blocks above, b = 3..0
+    for (int b = 3; b >= 0; --b) {
+        if (warp == b) {
+            float acc = 0.f;
+#pragma unroll 8
+            for (int k = 0; k < 32; ++k) acc = fmaf(sm.invT[b][k][lane], sm.v[32 * b + k], acc);
+            __syncwarp();
+            sm.v[32 * b + lane] = acc;
+        }
+        __syncthreads();
+        if (warp < b) {
+            float acc = sm.v[tid];
+#pragma unroll 8
+            for (int k = 0; k < 32; ++k) acc = fmaf(-sm.U[tid][32 * b + k], sm.v[32 * b + k], acc);
+            sm.v[tid] = acc;
+        }
+        __syncthreads();
+    }
+    if (tid < kNb) x[r * kNb + tid] = sm.v[tid];
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) st_release(flags + r, 1);
+}
+
+void launch_trsv_fused(const float* W, int ld, int np, float* x, int* ctrl, cudaStream_t s)
+{
+    const int nblk = np / kNb;
+    cudaMemsetAsync(ctrl, 0, (size_t)(nblk + 1) * sizeof(int), s);
+    trsv_fused_kernel<<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, np, x, ctrl);
+    ++g_launch_count;
+}
+
+// =====================================================================================
 // 6. Layout helpers
 // =====================================================================================
 __global__ void set_column_kernel(float* w, int ld, int col, const float* src, int nrows)
@@ -314,6 +456,7 @@ void simt_setup_device()
 {
     panel_setup_device();
     cudaFuncSetAttribute(trsv_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvDiagSmem);
+    cudaFuncSetAttribute(trsv_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TrsvSmem));
 }
 
 } // namespace gb200
