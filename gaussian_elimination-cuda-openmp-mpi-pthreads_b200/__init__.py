@@ -28,8 +28,9 @@ ABI_SYMBOLS = (
     "gauss_cuda_init", "gauss_cuda_unique_id", "gauss_cuda_init_dist", "gauss_cuda_solve",
     "gauss_cuda_upload", "gauss_cuda_solve_resident", "gauss_cuda_download",
     "gauss_cuda_compute_gauss", "gauss_cuda_solve_gauss", "gauss_cuda_download_factors",
-    "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device", "matmul_cuda_device_noalloc",
+    "gauss_cuda_set_pivoting", "gauss_cuda_get_pivots", "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device", "matmul_cuda_device_noalloc",
     "gauss_host_init_matrix", "gauss_host_initialize_inputs", "gauss_host_matmul_fill",
+    "gauss_host_read_dat", "gauss_host_init_rhs", "gauss_host_free",
     "gauss_cuda_strerror", "gauss_cuda_last_error", "gauss_cuda_device_count",
 )
 
@@ -84,6 +85,13 @@ def lib():
         L.gauss_cuda_solve_gauss.argtypes = [vp, C.POINTER(GaussStats)]
         L.gauss_cuda_download.argtypes = [vp, _fp, _fp]
         L.gauss_cuda_download_factors.argtypes = [vp, _fp]
+        L.gauss_cuda_set_pivoting.argtypes = [vp, C.c_int]
+        L.gauss_cuda_get_pivots.argtypes = [vp, C.POINTER(C.c_int)]
+        L.gauss_host_read_dat.argtypes = [C.c_char_p, C.POINTER(_dp)]
+        L.gauss_host_init_rhs.argtypes = [_dp, _dp, _dp, C.c_int]
+        L.gauss_host_init_rhs.restype = None
+        L.gauss_host_free.argtypes = [vp]
+        L.gauss_host_free.restype = None
         L.gauss_cuda_free.argtypes = [vp]
         L.gauss_cuda_free.restype = None
         L.matmul_cuda.argtypes = [_fp, _fp, _fp, C.c_int, C.c_int, _dp]
@@ -140,6 +148,26 @@ def initialize_inputs(nsize, seed=1):
     X = np.empty(nsize, np.float64)
     lib().gauss_host_initialize_inputs(A.ctypes.data_as(_dp), B.ctypes.data_as(_dp), X.ctypes.data_as(_dp), nsize, seed)
     return A, B, X
+
+
+def read_dat(fname):
+    """initMatrix(fname) of the external-input variant (gauss_external_input.c:32-84): dense double matrix."""
+    p = _dp()
+    n = lib().gauss_host_read_dat(os.fsencode(fname), C.byref(p))
+    if n < 0:
+        raise OSError("The matrix file open error")
+    A = np.ctypeslib.as_array(p, shape=(n, n)).copy()
+    lib().gauss_host_free(p)
+    return A
+
+
+def initRHS(A):
+    """initRHS (gauss_external_input.c:88-106): returns (R, X__) with X__ = 1..n and R = A X__."""
+    A = np.ascontiguousarray(A, np.float64)
+    n = A.shape[0]
+    R, Xp = np.empty(n), np.empty(n)
+    lib().gauss_host_init_rhs(A.ctypes.data_as(_dp), R.ctypes.data_as(_dp), Xp.ctypes.data_as(_dp), n)
+    return R, Xp
 
 
 def matmul_fill(nsize):
@@ -245,6 +273,15 @@ class GaussCuda:
         _check(lib().gauss_cuda_download(self._h, X.ctypes.data_as(_fp), Bo.ctypes.data_as(_fp) if want_b_after else None))
         return (X, Bo) if want_b_after else X
 
+    def set_pivoting(self, enabled=True):
+        """Partial pivoting as in the reference's external-input variant (gauss_external_input.c:123-148)."""
+        _check(lib().gauss_cuda_set_pivoting(self._h, 1 if enabled else 0))
+
+    def pivots(self):
+        piv = np.empty(self.n, np.int32)
+        _check(lib().gauss_cuda_get_pivots(self._h, piv.ctypes.data_as(C.POINTER(C.c_int))))
+        return piv
+
     def download_factors(self):
         LU = np.empty((self.n, self.n), np.float32)
         _check(lib().gauss_cuda_download_factors(self._h, LU.ctypes.data_as(_fp)))
@@ -268,9 +305,11 @@ class GaussCuda:
             pass
 
 
-def gauss(A, B, mode=MODE_3XTF32, nb=0, want_b_after=False):
+def gauss(A, B, mode=MODE_3XTF32, nb=0, want_b_after=False, pivoting=False):
     """One-shot gauss(): allocate, eliminate, back-substitute, free."""
     with GaussCuda(len(B), nb=nb, mode=mode) as g:
+        if pivoting:
+            g.set_pivoting(True)
         return g.gauss(A, B, want_b_after=want_b_after)
 
 

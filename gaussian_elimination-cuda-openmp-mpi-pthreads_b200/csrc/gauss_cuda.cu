@@ -137,8 +137,12 @@ struct gauss_cuda_ctx {
     float* hvec = nullptr;   // [np] staging for RHS upload / B_out
     int* status = nullptr;   // device: 0 or (row+1) of the first bad pivot
     int* trsv_ctrl = nullptr;   // device: ticket + per-128-block flags of the fused back substitution
+    bool pivot = false;         // partial pivoting (external-input variant)
+    float* pt = nullptr;        // packed panel scratch [128 x np]
+    int* ipiv = nullptr;        // device: pivot row of every step
     cudaStream_t s_main = nullptr, s_comm = nullptr;
     cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
+    cudaEvent_t ev_diag[2] = {nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> upd_ev;    // 2 per outer block: brackets of the trailing-update launches
     std::vector<double> upd_flops;
@@ -218,6 +222,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
             e = cudaEventCreateWithFlags(&c->ev_ready[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_diag[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_free[i], cudaEventDisableTiming);
         }
     }
@@ -268,11 +273,14 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     for (float* b : bufs) if (b) cudaFree(b);
     if (c->status) cudaFree(c->status);
     if (c->trsv_ctrl) cudaFree(c->trsv_ctrl);
+    if (c->pt) cudaFree(c->pt);
+    if (c->ipiv) cudaFree(c->ipiv);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->upd_ev) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         if (c->ev_ready[i]) cudaEventDestroy(c->ev_ready[i]);
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
+        if (c->ev_diag[i]) cudaEventDestroy(c->ev_diag[i]);
         if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
     }
     if (c->s_comm) cudaStreamDestroy(c->s_comm);
@@ -325,8 +333,8 @@ static int gemm_update(gauss_cuda_ctx* c, const float* A, int lda, const float* 
 
 // ---- the pieces of one outer step --------------------------------------------------------
 struct PanelRef {            // where the factored row panel of the current outer block can be read
-    const float* p;          // element (panel row 0, column k0)
-    int ld;
+    const float* pd; int ldd;       // its diagonal region: element (panel row 0, column k0), kb columns
+    const float* pu; int ldu;       // the U12 region:      element (panel row 0, column k0 + kb)
     float* ub_hi; float* ub_lo;     // split, transposed U operand of this step (3xTF32 mode)
 };
 
@@ -358,15 +366,24 @@ static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo)
     return GAUSS_CUDA_OK;
 }
 
-// Non-owners in 3xTF32 mode: rebuild the split, transposed U operand from the raw broadcast panel.
-static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr)
+// Non-owners in 3xTF32 mode: rebuild the split, transposed U operand from the raw broadcast panel;
+// `diag_part` selects the columns inside the panel (needed by P2) or right of it (needed by P3).
+static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr, bool diag_part)
 {
-    const int NB = c->NB, k0 = K * NB, ninner = blk_rows(c, K) / kNb;
+    const int NB = c->NB, k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
     for (int j = 0; j < ninner; ++j) {
-        const int r = j * kNb, cfirst = r + kNb;          // panel-relative first column right of inner block j
-        launch_split_transpose(pr.p + (size_t)r * pr.ld + cfirst, pr.ld,
-                               pr.ub_hi + (size_t)(k0 + cfirst) * NB + r, pr.ub_lo + (size_t)(k0 + cfirst) * NB + r,
-                               NB, kNb, c->ld - k0 - cfirst, kNb, c->s_main);
+        const int r = j * kNb;
+        if (diag_part) {
+            const int cfirst = r + kNb, ncol = kb - cfirst;        // panel-relative columns right of inner block j
+            if (ncol > 0)
+                launch_split_transpose(pr.pd + (size_t)r * pr.ldd + cfirst, pr.ldd,
+                                       pr.ub_hi + (size_t)(k0 + cfirst) * NB + r, pr.ub_lo + (size_t)(k0 + cfirst) * NB + r,
+                                       NB, kNb, ncol, kNb, c->s_main);
+        } else {
+            launch_split_transpose(pr.pu + (size_t)r * pr.ldu, pr.ldu,
+                                   pr.ub_hi + (size_t)(k0 + kb) * NB + r, pr.ub_lo + (size_t)(k0 + kb) * NB + r,
+                                   NB, kNb, c->ld - k0 - kb, kNb, c->s_main);
+        }
     }
 }
 
@@ -382,11 +399,11 @@ static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo)
     float* Wb = c->W + (size_t)row_lo * ld;
     for (int j = 0; j < ninner; ++j) {
         const int kk = k0 + j * kNb, r = j * kNb;
-        launch_lcol(pr.p + (size_t)r * pr.ld + r, pr.ld, Wb + kk, ld, m,
+        launch_lcol(pr.pd + (size_t)r * pr.ldd + r, pr.ldd, Wb + kk, ld, m,
                     tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr, NB, r, s);
         const int nin = kb - (r + kNb);                    // columns of the panel still to the right
         if (nin > 0) {
-            int rc = gemm_update(c, Wb + kk, ld, pr.p + (size_t)r * pr.ld + r + kNb, pr.ld,
+            int rc = gemm_update(c, Wb + kk, ld, pr.pd + (size_t)r * pr.ldd + r + kNb, pr.ldd,
                                  tc ? c->la_hi + (size_t)row_lo * NB + r : nullptr, tc ? c->la_lo + (size_t)row_lo * NB + r : nullptr,
                                  tc ? pr.ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? pr.ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
                                  Wb + kk + kNb, m, nin, kNb);
@@ -409,7 +426,7 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row
     const int ui = c->upd_count;
     const bool timed = (size_t)(2 * ui + 1) < c->upd_ev.size();
     if (timed) CK(cudaEventRecord(c->upd_ev[2 * ui], s));
-    int rc = gemm_update(c, Wb + k0, ld, pr.p + kb, pr.ld,
+    int rc = gemm_update(c, Wb + k0, ld, pr.pu, pr.ldu,
                          tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr,
                          tc ? pr.ub_hi + (size_t)(k0 + kb) * NB : nullptr, tc ? pr.ub_lo + (size_t)(k0 + kb) * NB : nullptr,
                          Wb + k0 + kb, m, ld - (k0 + kb), kb);
@@ -429,7 +446,8 @@ static int factor_single(gauss_cuda_ctx* c)
     for (int K = 0; K < c->nblk; ++K) {
         int rc = panel_factor(c, K, c->ub_hi[0], c->ub_lo[0]);
         if (rc) return rc;
-        PanelRef pr{c->W + (size_t)blk_local_row(c, K) * ld + K * NB, ld, c->ub_hi[0], c->ub_lo[0]};
+        const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + K * NB;
+        PanelRef pr{P0, ld, P0 + blk_rows(c, K), ld, c->ub_hi[0], c->ub_lo[0]};
         const int l0 = first_local_block_after(c, K) * NB;
         if ((rc = col_panel(c, K, pr, l0))) return rc;
         if ((rc = trailing_update(c, K, pr, l0, c->rows_local))) return rc;
@@ -447,18 +465,25 @@ static int factor_lookahead(gauss_cuda_ctx* c)
     const int ld = c->ld, NB = c->NB;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     auto owner_of = [&](int K) { return K % c->world; };
-    // enqueue on the comm stream: (owner) pack panel K, then broadcast it into pbuf[K&1]
+    // enqueue on the comm stream: (owner) pack panel K, then broadcast it into pbuf[K&1] in two pieces --
+    // the kb x kb diagonal region first (all that P2 needs), then the U12 region (needed by P3)
     auto enqueue_bcast = [&](int K) -> int {
-        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K), ldp = ld - k0;
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K), ldu = ld - k0 - kb;
+        float* bufd = c->pbuf[b];
+        float* bufu = c->pbuf[b] + (size_t)kb * kb;
         CK(cudaStreamWaitEvent(sc, c->ev_free[b], 0));            // last readers of pbuf[b] are done
         if (owner_of(K) == c->rank) {
             CK(cudaStreamWaitEvent(sc, c->ev_ready[b], 0));       // P1(K) finished on the main stream
             const float* P = c->W + (size_t)blk_local_row(c, K) * ld + k0;
-            CK(cudaMemcpy2DAsync(c->pbuf[b], (size_t)ldp * sizeof(float), P, (size_t)ld * sizeof(float),
-                                 (size_t)ldp * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
+            CK(cudaMemcpy2DAsync(bufd, (size_t)kb * sizeof(float), P, (size_t)ld * sizeof(float),
+                                 (size_t)kb * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
+            CK(cudaMemcpy2DAsync(bufu, (size_t)ldu * sizeof(float), P + kb, (size_t)ld * sizeof(float),
+                                 (size_t)ldu * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
         }
-        NK(g_nccl.Broadcast(c->pbuf[b], c->pbuf[b], (size_t)kb * ldp, ncclFloat, owner_of(K), c->comm, sc));
-        if (owner_of(K) != c->rank) c->bcast_bytes += (double)kb * ldp * sizeof(float);
+        NK(g_nccl.Broadcast(bufd, bufd, (size_t)kb * kb, ncclFloat, owner_of(K), c->comm, sc));
+        CK(cudaEventRecord(c->ev_diag[b], sc));
+        NK(g_nccl.Broadcast(bufu, bufu, (size_t)kb * ldu, ncclFloat, owner_of(K), c->comm, sc));
+        if (owner_of(K) != c->rank) c->bcast_bytes += (double)kb * (kb + ldu) * sizeof(float);
         CK(cudaEventRecord(c->ev_done[b], sc));
         return GAUSS_CUDA_OK;
     };
@@ -474,16 +499,22 @@ static int factor_lookahead(gauss_cuda_ctx* c)
     for (int K = 0; K < c->nblk; ++K) {
         const int b = K & 1, k0 = K * NB;
         const bool mine = owner_of(K) == c->rank;
+        const int kb = blk_rows(c, K);
         PanelRef pr;
         if (mine) {                                               // the owner reads its panel in place
-            pr = PanelRef{c->W + (size_t)blk_local_row(c, K) * ld + k0, ld, c->ub_hi[b], c->ub_lo[b]};
+            const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+            pr = PanelRef{P0, ld, P0 + kb, ld, c->ub_hi[b], c->ub_lo[b]};
         } else {
-            CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));
-            pr = PanelRef{c->pbuf[b], ld - k0, c->ub_hi[b], c->ub_lo[b]};
-            if (tc) rebuild_split_u(c, K, pr);
+            pr = PanelRef{c->pbuf[b], kb, c->pbuf[b] + (size_t)kb * kb, ld - k0 - kb, c->ub_hi[b], c->ub_lo[b]};
+            CK(cudaStreamWaitEvent(s, c->ev_diag[b], 0));         // the diagonal region has arrived
+            if (tc) rebuild_split_u(c, K, pr, true);
         }
         const int l0 = first_local_block_after(c, K) * NB;
         if ((rc = col_panel(c, K, pr, l0))) return rc;
+        if (!mine) {
+            CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // ... and now the U12 region
+            if (tc) rebuild_split_u(c, K, pr, false);
+        }
         int rest_lo = l0;
         if (K + 1 < c->nblk) {
             if (owner_of(K + 1) == c->rank) {
@@ -504,12 +535,40 @@ static int factor_lookahead(gauss_cuda_ctx* c)
     return GAUSS_CUDA_OK;
 }
 
+// Partial pivoting (gauss_external_input.c:123-182): single-level blocking, one 128-column panel at a
+// time -- pivoted panel factorisation over all rows below, interchanges applied to the right-hand part,
+// U-row solve, rank-128 trailing update (the no-pivot kernels from there on).
+static int factor_pivot(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main;
+    const int ld = c->ld, NB = c->NB, np = c->np;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    for (int k0 = 0; k0 < np; k0 += kNb) {
+        const int below = k0 + kNb;
+        launch_panel_pivot(c->W, ld, np, k0, c->pt, np, c->ipiv, c->status,
+                           tc ? c->la_hi + (size_t)below * NB : nullptr, tc ? c->la_lo + (size_t)below * NB : nullptr, NB, s);
+        float* P = c->W + (size_t)k0 * ld;
+        launch_urow(P + k0, ld, P + below, ld, np + 1 - below,
+                    tc ? c->ub_hi[0] + (size_t)below * NB : nullptr, tc ? c->ub_lo[0] + (size_t)below * NB : nullptr, NB, 0, s);
+        const int m = np - below;
+        if (m > 0) {
+            float* Wb = c->W + (size_t)below * ld;
+            int rc = gemm_update(c, Wb + k0, ld, P + below, ld,
+                                 tc ? c->la_hi + (size_t)below * NB : nullptr, tc ? c->la_lo + (size_t)below * NB : nullptr,
+                                 tc ? c->ub_hi[0] + (size_t)below * NB : nullptr, tc ? c->ub_lo[0] + (size_t)below * NB : nullptr,
+                                 Wb + below, m, ld - below, kNb);
+            if (rc) return rc;
+        }
+    }
+    return GAUSS_CUDA_OK;
+}
+
 static int factor(gauss_cuda_ctx* c)
 {
     CK(cudaMemsetAsync(c->status, 0, sizeof(int), c->s_main));
     c->bcast_bytes = 0.0;
     c->upd_count = 0;
-    int rc = c->world > 1 ? factor_lookahead(c) : factor_single(c);
+    int rc = c->pivot ? factor_pivot(c) : (c->world > 1 ? factor_lookahead(c) : factor_single(c));
     if (rc) return rc;
     CK(cudaGetLastError());
     c->factored = true;
@@ -523,30 +582,20 @@ static int backsub(gauss_cuda_ctx* c)
     cudaStream_t s = c->s_main;
     const int ld = c->ld, NB = c->NB, np = c->np;
     if (c->world == 1) {                   // one launch; U is streamed once, W stays untouched
-        launch_trsv_fused(c->W, ld, np, c->xvec, c->trsv_ctrl, s);
+        launch_trsv_fused(c->W, ld, np, np, c->xvec, c->trsv_ctrl, s);
         CK(cudaGetLastError());
         return GAUSS_CUDA_OK;
     }
     for (int K = c->nblk - 1; K >= 0; --K) {
         const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
-        const int ninner = kb / kNb;
-        if (owner == c->rank) {
-            float* P = c->W + (size_t)blk_local_row(c, K) * ld;
-            for (int j = ninner - 1; j >= 0; --j) {
-                const int kk = k0 + j * kNb, r = j * kNb;
-                launch_trsv_diag(P + (size_t)r * ld + kk, ld, np - kk, c->xvec + kk, s);
-                launch_trsv_gemv(P + kk, ld, np - kk, c->xvec + kk, r, s);      // panel rows above this inner block
-            }
+        if (owner == c->rank) {                    // the owner's kb x kb diagonal system, one fused launch
+            const float* P = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+            launch_trsv_fused(P, ld, kb, np - k0, c->xvec + k0, c->trsv_ctrl, s);
         }
-        if (c->world > 1) {
-            NK(g_nccl.Broadcast(c->xvec + k0, c->xvec + k0, (size_t)kb, ncclFloat, owner, c->comm, s));
-            if (owner != c->rank) c->bcast_bytes += (double)kb * sizeof(float);
-        }
+        NK(g_nccl.Broadcast(c->xvec + k0, c->xvec + k0, (size_t)kb, ncclFloat, owner, c->comm, s));
+        if (owner != c->rank) c->bcast_bytes += (double)kb * sizeof(float);
         const int mabove = local_blocks_before(c, K) * NB;
-        for (int j = 0; j < ninner && mabove > 0; ++j) {
-            const int kk = k0 + j * kNb;
-            launch_trsv_gemv(c->W + kk, ld, np - kk, c->xvec + kk, mabove, s);
-        }
+        launch_trsv_gemv_wide(c->W + k0, ld, np - k0, c->xvec + k0, mabove, kb, s);
     }
     CK(cudaGetLastError());
     return GAUSS_CUDA_OK;
@@ -711,6 +760,31 @@ extern "C" int gauss_cuda_download(gauss_cuda_ctx* c, float* X, float* B_out)
     int rc = download_results(c, X, B_out);
     if (rc) return rc;
     CK(cudaStreamSynchronize(c->s_main));
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int gauss_cuda_set_pivoting(gauss_cuda_ctx* c, int enabled)
+{
+    if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (c->world != 1) { snprintf(g_err, sizeof g_err, "partial pivoting is a single-GPU path"); return GAUSS_CUDA_BAD_ARG; }
+    CK(cudaSetDevice(c->device));
+    if (enabled && !c->pt) {
+        CK(cudaMalloc((void**)&c->pt, (size_t)kNb * c->np * sizeof(float)));
+        CK(cudaMalloc((void**)&c->ipiv, (size_t)c->np * sizeof(int)));
+        CK(cudaMemset(c->ipiv, 0, (size_t)c->np * sizeof(int)));
+    }
+    c->pivot = enabled != 0;
+    c->factored = false;
+    return GAUSS_CUDA_OK;
+}
+
+extern "C" int gauss_cuda_get_pivots(gauss_cuda_ctx* c, int* pivot_rows)
+{
+    if (!c || !pivot_rows) return GAUSS_CUDA_BAD_ARG;
+    if (!c->ipiv) return GAUSS_CUDA_NOT_READY;
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->s_main));
+    CK(cudaMemcpy(pivot_rows, c->ipiv, (size_t)c->n * sizeof(int), cudaMemcpyDeviceToHost));
     return GAUSS_CUDA_OK;
 }
 

@@ -39,9 +39,11 @@ void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C,
 //              column `ycol` of the same rows (ycol relative to ukk), x also written back there.
 //  trsv_gemv:  y[r] -= U[r, blk] . x  for `nrows` rows starting at `u` (ld), y at column offset ycol.
 void launch_trsv_diag(float* ukk, int ld, int ycol, float* x, cudaStream_t s);
-// Whole back substitution of an [np x ld] factored system in one launch: x = U^-1 * W[:, np].
-// ctrl: np/128 + 1 ints of device scratch (ticket + per-block flags), reset here.  W is not modified.
-void launch_trsv_fused(const float* W, int ld, int np, float* x, int* ctrl, cudaStream_t s);
+// Whole back substitution of an [nrows x nrows] unit-upper system in one launch: x = U^-1 * W[:, ycol]
+// (W points at the system's element (0,0); ycol is relative to it).  ctrl: nrows/128 + 1 ints of device
+// scratch (ticket + per-block flags), reset here.  W is not modified.
+void launch_trsv_fused(const float* W, int ld, int nrows, int ycol, float* x, int* ctrl, cudaStream_t s);
+void launch_trsv_gemv_wide(float* u, int ld, int ycol, const float* x, int nrows, int kw, cudaStream_t s);
 void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cudaStream_t s);
 
 // Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.
@@ -56,6 +58,13 @@ void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int
 void simt_setup_device();     // per-device dynamic shared memory opt-ins of the SIMT kernels
 void panel_setup_device();    // same for lu_panel.cu (called by simt_setup_device)
 int  tc_setup_device();       // same for the tile engine; returns a GAUSS_CUDA_* status
+
+// ---- partial-pivoting panel (lu_pivot.cu) --------------------------------------------------
+// Factors the panel W[k0.., k0..k0+128) of an [np x ld] single-GPU system with row interchanges
+// (gauss_external_input.c:123-148, 161-181); see lu_pivot.cu.  la_* (may be null): split of the rows
+// below the diagonal block, la[(i-128)*ldla + c].
+void launch_panel_pivot(float* W, int ld, int np, int k0, float* pt, int mp, int* ipiv, int* status,
+                        float* la_hi, float* la_lo, int ldla, cudaStream_t s);
 
 // ---- tensor-core tile engine (tc_gemm.cu) -----------------------------------------------
 

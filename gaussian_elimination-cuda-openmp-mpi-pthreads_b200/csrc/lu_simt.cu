@@ -239,12 +239,12 @@ __device__ __forceinline__ void st_release(int* p, int v) {
 }
 
 __global__ void __launch_bounds__(256, 1)
-trsv_fused_kernel(const float* __restrict__ W, int ld, int np, float* __restrict__ x, int* __restrict__ ctrl)
+trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, float* __restrict__ x, int* __restrict__ ctrl)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     TrsvSmem& sm = *reinterpret_cast<TrsvSmem*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int nblk = np / kNb;
+    const int nblk = nrows / kNb;
     if (tid == 0) sm.ticket = atomicAdd(&ctrl[0], 1);
     __syncthreads();
     const int r = nblk - 1 - sm.ticket;      // my row block; every block J > r belongs to an earlier ticket
@@ -256,7 +256,7 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int np, float* __restrict
         const int rr = idx >> 5, c4 = (idx & 31) << 2;
         *reinterpret_cast<float4*>(&sm.U[rr][c4]) = __ldg(reinterpret_cast<const float4*>(Wr + (size_t)rr * ld + r * kNb + c4));
     }
-    if (tid < kNb) sm.v[tid] = Wr[(size_t)tid * ld + np];
+    if (tid < kNb) sm.v[tid] = Wr[(size_t)tid * ld + ycol];
 
     // rows 16*warp .. 16*warp+15 of the block; per-lane partial dot products over the lane's 4 columns
     float part[16];
@@ -345,11 +345,47 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int np, float* __restrict
     if (tid == 0) st_release(flags + r, 1);
 }
 
-void launch_trsv_fused(const float* W, int ld, int np, float* x, int* ctrl, cudaStream_t s)
+void launch_trsv_fused(const float* W, int ld, int nrows, int ycol, float* x, int* ctrl, cudaStream_t s)
 {
-    const int nblk = np / kNb;
+    const int nblk = nrows / kNb;
     cudaMemsetAsync(ctrl, 0, (size_t)(nblk + 1) * sizeof(int), s);
-    trsv_fused_kernel<<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, np, x, ctrl);
+    trsv_fused_kernel<<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, nrows, ycol, x, ctrl);
+    ++g_launch_count;
+}
+
+// y[r] -= U[r, 0..kw) . x[0..kw)  for nrows rows (kw a multiple of 128): the wide form of trsv_gemv, one
+// launch per outer block in the multi-GPU back substitution.  A warp takes 4 rows, float4 per lane.
+__global__ void __launch_bounds__(256)
+trsv_gemv_wide_kernel(float* __restrict__ u, int ld, int ycol, const float* __restrict__ x, int nrows, int kw)
+{
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    const int r0 = (blockIdx.x * 8 + wrp) * 4;
+    float s_[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < kw; c += kNb) {
+        const float4 xv = __ldg(reinterpret_cast<const float4*>(x + c + 4 * lane));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (r0 + i < nrows) {
+                const float4 v = __ldcs(reinterpret_cast<const float4*>(u + (size_t)(r0 + i) * ld + c + 4 * lane));
+                s_[i] = fmaf(v.x, xv.x, s_[i]); s_[i] = fmaf(v.y, xv.y, s_[i]);
+                s_[i] = fmaf(v.z, xv.z, s_[i]); s_[i] = fmaf(v.w, xv.w, s_[i]);
+            }
+        }
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) s_[i] += __shfl_xor_sync(0xffffffffu, s_[i], off);
+    if (lane < 4 && r0 + lane < nrows) {
+        const float mine = lane == 0 ? s_[0] : lane == 1 ? s_[1] : lane == 2 ? s_[2] : s_[3];
+        u[(size_t)(r0 + lane) * ld + ycol] -= mine;
+    }
+}
+
+void launch_trsv_gemv_wide(float* u, int ld, int ycol, const float* x, int nrows, int kw, cudaStream_t s)
+{
+    if (nrows <= 0 || kw <= 0) return;
+    trsv_gemv_wide_kernel<<<(nrows + 31) / 32, 256, 0, s>>>(u, ld, ycol, x, nrows, kw);
     ++g_launch_count;
 }
 

@@ -149,13 +149,30 @@ __device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t saddr)
     return d;
 }
 
+// Tile rasterisation.  Tiles are walked in bands of kBandN tile-columns, row-major inside a band, so
+// the ~148 tiles in flight cover a compact (about 9 x 16) patch: the band's B slab (16 x 256 rows of
+// split U, 16 MB at K = 512) and the patch's A tiles stay L2-resident while C streams through.
+// (Plain row-major order re-streamed all of B for every tile row: 3.4x read amplification at N = 32768.)
+constexpr int kBandN = 16;
+__device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int& m0, int& n0)
+{
+    const int band_tiles = num_m * kBandN;
+    const int band = t / band_tiles;
+    const int in_band = t - band * band_tiles;
+    const int wb = min(kBandN, num_n - band * kBandN);      // the last band may be narrower
+    const int mi = in_band / wb;
+    const int ni = band * kBandN + (in_band - mi * wb);
+    m0 = mi * TBM;
+    n0 = ni * TBN;
+}
+
 // ---------------------------------------------------------------------------- the kernel
 template <int BK, int STAGES>
 __global__ void __launch_bounds__(kTcThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant__ CUtensorMap tm_alo,
                const __grid_constant__ CUtensorMap tm_bhi, const __grid_constant__ CUtensorMap tm_blo,
                const __grid_constant__ CUtensorMap tm_c,
-               int m, int n, int k, int negate, int reduce)
+               int m, int n, int k, int negate, int reduce, int* __restrict__ sched)
 {
     using Cfg = TcCfg<BK, STAGES>;
     extern __shared__ unsigned char smem_dyn[];
@@ -166,16 +183,22 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
     auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    // dynamic tile scheduler: a 4-deep queue of tile indices, producer -> {MMA issuer, epilogue}
+    auto qfull_bar = [&](int q) { return bar_base + 8u * (2 * STAGES + 5 + q); };
+    auto qempty_bar = [&](int q) { return bar_base + 8u * (2 * STAGES + 9 + q); };
     unsigned char* gen_base = smem_dyn + (base - smem_u32(smem_dyn));
+    volatile int* q_tile = reinterpret_cast<volatile int*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 13));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_n = (n + TBN - 1) / TBN;
-    const int num_tiles = ((m + TBM - 1) / TBM) * num_n;
+    const int num_m = (m + TBM - 1) / TBM;
+    const int num_tiles = num_m * num_n;
     const int num_kb = k / BK;
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 128); }
+        for (int q = 0; q < 4; ++q) { mbar_init(qfull_bar(q), 1); mbar_init(qempty_bar(q), 1 + 128); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -191,8 +214,18 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
         // ===================== TMA producer =====================
         if (elect_one()) {
             int stage = 0; uint32_t phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-                const int m0 = (t / num_n) * TBM, n0 = (t % num_n) * TBN;
+            // first tile is static (blockIdx.x); later ones come from a global counter, so a CTA that
+            // gets its SM late (or shares the GPU with another stream's kernels) simply takes fewer tiles
+            for (int it = 0;; ++it) {
+                const int q = it & 3;
+                int t = it == 0 ? (int)blockIdx.x : atomicAdd(sched, 1) + (int)gridDim.x;
+                if (t >= num_tiles) t = -1;
+                mbar_wait(qempty_bar(q), ((it >> 2) & 1) ^ 1);
+                q_tile[q] = t;
+                mbar_arrive(qfull_bar(q));                  // release: the tile index is visible to the consumers
+                if (t < 0) break;
+                int m0, n0;
+                tile_coords(t, num_m, num_n, m0, n0);
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1);
                     const uint32_t sa = base + stage * Cfg::stage_bytes;
@@ -212,8 +245,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((negate ? 1u : 0u) << 13) |
                                    ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
-            int it = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
+            for (int it = 0;; ++it) {
+                const int q = it & 3;
+                mbar_wait(qfull_bar(q), (it >> 2) & 1);
+                const int t = q_tile[q];
+                mbar_arrive(qempty_bar(q));
+                if (t < 0) break;
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 mbar_wait(tempty_bar(as), aphase ^ 1);
@@ -245,10 +282,15 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
         const int q = warp & 3;                             // TMEM lane quarter this warp may touch
         const int row = q * 32 + lane;
         const bool issuer = (threadIdx.x == 64);
-        int it = 0;
         int cbuf = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++it) {
-            const int m0 = (t / num_n) * TBM, n0 = (t % num_n) * TBN;
+        for (int it = 0;; ++it) {
+            const int q = it & 3;
+            mbar_wait(qfull_bar(q), (it >> 2) & 1);
+            const int t = q_tile[q];
+            mbar_arrive(qempty_bar(q));
+            if (t < 0) break;
+            int m0, n0;
+            tile_coords(t, num_m, num_n, m0, n0);
             const int as = it & 1;
             const uint32_t aphase = (it >> 1) & 1;
             mbar_wait(tfull_bar(as), aphase);
@@ -290,6 +332,11 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
+    // the last CTA to leave rearms the scheduler slot for a later launch (sched[0] tile counter, sched[1] exits)
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) { sched[0] = 0; sched[1] = 0; __threadfence(); }
+    }
 }
 
 // ---------------------------------------------------------------------------- host side
@@ -299,6 +346,14 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
 static EncodeTiledFn g_encode = nullptr;
 static int g_variant = 0;            // 0: BK=32, 2 stages (128 B swizzle); 1: BK=16, 4 stages (64 B swizzle)
 static int g_num_sms = 0;
+// Scheduler slots: {tile counter, exit counter} pairs in a file-scope device array (zero at load, rearmed by
+// each launch's last CTA).  Launches rotate through the slots so that kernels in flight on different
+// streams never share one.  A static array rather than cudaMalloc: matmul_cuda_device_noalloc relies on it.
+constexpr int kSchedSlots = 64;
+static __device__ int g_sched_slots[2 * kSchedSlots];
+static int* g_sched_addr[16] = {nullptr};
+static unsigned g_sched_next = 0;
+static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
 
 bool tc_available()
 {
@@ -318,9 +373,16 @@ int tc_setup_device()
     }
     const char* v = getenv("GAUSS_CUDA_TC_VARIANT");
     if (v) g_variant = atoi(v) ? 1 : 0;
+    const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
+    if (rs) g_reserve_sms = atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs));
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (dev >= 0 && dev < 16 && !g_sched_addr[dev]) {
+        int* p = nullptr;
+        if (cudaGetSymbolAddress((void**)&p, g_sched_slots) != cudaSuccess) return GAUSS_CUDA_CUDA_ERR;
+        g_sched_addr[dev] = p;
+    }
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<32, 2>::smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_gemm_kernel<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<16, 4>::smem_bytes);
     return e == cudaSuccess ? GAUSS_CUDA_OK : GAUSS_CUDA_CUDA_ERR;
@@ -354,8 +416,13 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     rc |= make_map(&tc, C, n, m, ldc, TEPI_W, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return (int)cudaErrorInvalidValue;
     const int tiles = ((m + TBM - 1) / TBM) * ((n + TBN - 1) / TBN);
-    const int grid = tiles < g_num_sms ? tiles : g_num_sms;
-    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0);
+    const int avail = g_num_sms - g_reserve_sms;
+    const int grid = tiles < avail ? tiles : avail;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
+    int* sched = g_sched_addr[dev] + 2 * (g_sched_next++ % kSchedSlots);
+    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched);
     ++g_launch_count;
     return (int)cudaGetLastError();
 }

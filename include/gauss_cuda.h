@@ -108,6 +108,15 @@ int gauss_cuda_solve_gauss(gauss_cuda_ctx *ctx, gauss_cuda_stats *st);
  * LU: host, row-major n*n.  Single-GPU contexts only. */
 int gauss_cuda_download_factors(gauss_cuda_ctx *ctx, float *LU);
 
+/* Partial pivoting, the reference's EXTERNAL-input variant (gauss_openmp/gauss_external_input.c:123-148
+ * getPivot: the row with the largest |a[i][cur]|, i >= cur, is swapped in; :161-169 the pivot row is
+ * divided by the pivot).  enabled != 0 switches every later solve of this context to it; single-GPU
+ * contexts only (GAUSS_CUDA_BAD_ARG otherwise).  A zero column is reported as GAUSS_CUDA_ZERO_PIVOT
+ * (the reference prints "The matrix is singular", :133-136).  gauss_cuda_get_pivots returns, for every
+ * pivot step i < n, the row that was swapped into position i during the last elimination. */
+int gauss_cuda_set_pivoting(gauss_cuda_ctx *ctx, int enabled);
+int gauss_cuda_get_pivots(gauss_cuda_ctx *ctx, int *pivot_rows /* host, n */);
+
 void gauss_cuda_free(gauss_cuda_ctx *ctx);
 
 /* ---- FP32 matrix multiply -------------------------------------------------------------- */
@@ -150,6 +159,13 @@ void gauss_host_init_matrix(double *A, double *B, int n);
 void gauss_host_initialize_inputs(double *A, double *B, double *X_true, int n, unsigned seed);
 /* cuda_matmul.cu:126-132: A[idx] = idx+1, B[idx] = 1/(idx+1). */
 void gauss_host_matmul_fill(float *A, float *B, int n);
+/* initMatrix(fname) of the external-input variant (gauss_external_input.c:32-84): "rows cols nnz" header, then
+ * 1-based "row col value" lines up to a line with row 0.  Returns the order n (>0) and a malloc'd dense row-major
+ * matrix in *A_out (release with gauss_host_free), or -1 when the file cannot be read (the reference exits). */
+int  gauss_host_read_dat(const char *fname, double **A_out);
+/* initRHS (gauss_external_input.c:88-106): X_pre[i] = i+1, R = A * X_pre. */
+void gauss_host_init_rhs(const double *A, double *R, double *X_pre, int n);
+void gauss_host_free(void *p);
 
 /* ---- diagnostics ------------------------------------------------------------------------- */
 const char *gauss_cuda_strerror(int status);

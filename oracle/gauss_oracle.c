@@ -278,3 +278,104 @@ double oracle_max_rel_diff_f32(const float *X, const float *Y, size_t count)
     }
     return worst;
 }
+
+/* ---- external-input variant: coordinate files, partial pivoting (OE) ----------------------- */
+#include <stdio.h>
+
+/* initMatrix(fname), OE:32-84: first line "rows cols nnz" (only rows is used), then "row col value"
+ * lines, 1-based, until a line whose row is 0.  Returns the order n and a malloc'd dense row-major
+ * matrix in *A_out (caller frees), or -1 if the file cannot be opened (the reference exits). */
+int oracle_read_dat(const char *fname, double **A_out)
+{
+    FILE *f = fopen(fname, "r");
+    if (!f) return -1;
+    char line[1024];
+    int a = 0, b = 0, c = 0;
+    if (!fgets(line, sizeof line, f) || sscanf(line, "%d %d %d", &a, &b, &c) < 1 || a <= 0) { fclose(f); return -1; }
+    const int n = a;
+    double *A = (double *)calloc((size_t)n * n, sizeof(double));
+    if (!A) { fclose(f); return -1; }
+    while (fgets(line, sizeof line, f)) {
+        int r = 0, col = 0;
+        double v = 0.0;
+        sscanf(line, "%d %d %lf", &r, &col, &v);
+        if (r == 0) break;
+        A[(size_t)(r - 1) * n + (col - 1)] = v;
+    }
+    fclose(f);
+    *A_out = A;
+    return n;
+}
+
+/* initRHS, OE:88-106: X__[i] = i+1, R = A * X__ accumulated in ascending j. */
+void oracle_init_rhs(const double *A, double *R, double *Xpre, int n)
+{
+    for (int i = 0; i < n; ++i) Xpre[i] = (double)(i + 1);
+    for (int i = 0; i < n; ++i) {
+        double acc = 0.0;
+        for (int j = 0; j < n; ++j) acc += A[(size_t)i * n + j] * Xpre[j];
+        R[i] = acc;
+    }
+}
+
+/* getPivot with partial pivoting, OE:123-148: the row with the largest |a[i][cur]|, i >= cur (first one wins
+ * ties, strict >), is swapped in (tails [cur, n) and R); a zero column is singular. */
+int oracle_get_pivot_partial(double *A, double *R, int n, int cur, int *chosen)
+{
+    int pr = cur;
+    for (int i = cur + 1; i < n; ++i)
+        if (fabs(A[(size_t)i * n + cur]) > fabs(A[(size_t)pr * n + cur])) pr = i;
+    if (chosen) *chosen = pr;
+    if (fabs(A[(size_t)pr * n + cur]) == 0.0) return ORACLE_SINGULAR;
+    if (pr != cur) {
+        for (int c = cur; c < n; ++c) { double t = A[(size_t)pr * n + c]; A[(size_t)pr * n + c] = A[(size_t)cur * n + c]; A[(size_t)cur * n + c] = t; }
+        double t = R[pr]; R[pr] = R[cur]; R[cur] = t;
+    }
+    return ORACLE_OK;
+}
+
+/* computeGauss of the pivoting variant, OE:153-182: pivot, scale the pivot row (OE:161-169), eliminate
+ * (OE:172-181).  perm (may be NULL) receives the pivot row chosen at every step. */
+int oracle_compute_gauss_pivot(double *A, double *R, int *perm, int n, int nthreads)
+{
+#ifdef _OPENMP
+    if (nthreads > 0) omp_set_num_threads(nthreads);
+#else
+    (void)nthreads;
+#endif
+    for (int i = 0; i < n; ++i) {
+        int rc = oracle_get_pivot_partial(A, R, n, i, perm ? perm + i : NULL);
+        if (rc != ORACLE_OK) return rc;
+        double *pi = A + (size_t)i * n;
+        const double piv = pi[i];
+        if (piv != 1.0) {
+            pi[i] = 1.0;
+            for (int j = i + 1; j < n; ++j) pi[j] /= piv;
+            R[i] /= piv;
+        }
+        const double ri = R[i];
+#pragma omp parallel for schedule(static)
+        for (int j = i + 1; j < n; ++j) {
+            double *pj = A + (size_t)j * n;
+            const double m = pj[i];
+            pj[i] = 0.0;
+            for (int k = i + 1; k < n; ++k) pj[k] -= m * pi[k];
+            R[j] -= m * ri;
+        }
+    }
+    return ORACLE_OK;
+}
+
+/* Whole external-input solve: elimination with pivoting + solveGauss (OE:186-205, same recurrence as OI's). */
+int oracle_gauss_pivot(double *A, double *R, double *X, int n, int nthreads)
+{
+    int rc = oracle_compute_gauss_pivot(A, R, NULL, n, nthreads);
+    if (rc != ORACLE_OK) return rc;
+    X[n - 1] = R[n - 1];
+    for (int i = n - 2; i >= 0; --i) {
+        double v = R[i];
+        for (int j = n - 1; j > i; --j) v -= A[(size_t)i * n + j] * X[j];
+        X[i] = v;
+    }
+    return ORACLE_OK;
+}

@@ -59,6 +59,10 @@ def oracle():
         lib.oracle_matmul_f64.argtypes = [_fp, _fp, _dp, C.c_int]
         lib.oracle_max_rel_diff_f32.argtypes = [_fp, _fp, C.c_size_t]
         lib.oracle_max_rel_diff_f32.restype = C.c_double
+        lib.oracle_read_dat.argtypes = [C.c_char_p, C.POINTER(_dp)]
+        lib.oracle_init_rhs.argtypes = [_dp, _dp, _dp, C.c_int]
+        lib.oracle_compute_gauss_pivot.argtypes = [_dp, _dp, _ip, C.c_int, C.c_int]
+        lib.oracle_gauss_pivot.argtypes = [_dp, _dp, _dp, C.c_int, C.c_int]
         _oracle = lib
     return _oracle
 
@@ -136,6 +140,47 @@ def matmul_f64(A, B):
     Cm = np.empty((n, n), np.float64)
     oracle().oracle_matmul_f64(_ptr(A, _fp), _ptr(B, _fp), _ptr(Cm, _dp), n)
     return Cm
+
+
+# ---- external-input variant (coordinate files, partial pivoting) ------------
+
+def read_dat(path):
+    """oracle_read_dat: the reference's initMatrix(fname) (gauss_external_input.c:32-84) -> dense double matrix."""
+    p = _dp()
+    n = oracle().oracle_read_dat(os.fsencode(path), C.byref(p))
+    if n < 0:
+        raise OSError("The matrix file open error")
+    A = np.ctypeslib.as_array(p, shape=(n, n)).copy()
+    C.CDLL(None).free(p)
+    return A
+
+
+def init_rhs(A):
+    """initRHS (gauss_external_input.c:88-106): X__ = 1..n, R = A X__."""
+    A = np.ascontiguousarray(A, np.float64)
+    n = A.shape[0]
+    R, Xp = np.empty(n), np.empty(n)
+    oracle().oracle_init_rhs(_ptr(A, _dp), _ptr(R, _dp), _ptr(Xp, _dp), n)
+    return R, Xp
+
+
+def gauss_pivot(A, R, nthreads=1):
+    """Partial-pivoting computeGauss + solveGauss (gauss_external_input.c:123-205) on copies; returns X."""
+    A = np.array(A, np.float64, order="C")
+    R = np.array(R, np.float64)
+    n = R.shape[0]
+    X = np.empty(n)
+    rc = oracle().oracle_gauss_pivot(_ptr(A, _dp), _ptr(R, _dp), _ptr(X, _dp), n, nthreads)
+    if rc != 0:
+        raise ZeroDivisionError("The matrix is singular")
+    return X
+
+
+def coo_to_dense(npz, name):
+    n = int(npz[f"{name}_n"])
+    A = np.zeros((n, n))
+    A[npz[f"{name}_rows"], npz[f"{name}_cols"]] = npz[f"{name}_vals"]       # later entries win, like the parser
+    return A
 
 
 # ---- the reference's own object code --------------------------------------

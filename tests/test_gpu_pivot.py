@@ -1,0 +1,105 @@
+"""GPU parity of the partial-pivoting path (the reference's external-input variant,
+gauss_openmp/gauss_external_input.c) against the oracle, through the C ABI."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from _pkg import pkg, ROOT
+
+pytestmark = pytest.mark.gpu
+MODES = [pkg.MODE_FFMA, pkg.MODE_3XTF32]
+TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def external():
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "external_vectors.npz"))
+
+
+def permuted_system(n, seed):
+    """Well-conditioned but useless without pivoting: a diagonally dominant matrix with its rows shuffled."""
+    rng = np.random.default_rng(seed)
+    D = rng.uniform(-1, 1, (n, n))
+    D[np.arange(n), np.arange(n)] = np.sign(rng.uniform(-1, 1, n)) * (np.abs(D).sum(axis=1) + 1.0)
+    perm = rng.permutation(n)
+    A = D[perm]
+    R, Xpre = ol.init_rhs(A)
+    return A, R, Xpre
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n,seed", [(10, 1), (129, 2), (500, 3), (1100, 4)])
+def test_permuted_dominant_matches_oracle(n, seed, mode):
+    A, R, Xpre = permuted_system(n, seed)
+    Xo = ol.gauss_pivot(A, R, nthreads=4)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        with pytest.raises(pkg.GaussCudaError):
+            g.pivots()                                     # nothing to report before pivoting is switched on
+        g.set_pivoting(True)
+        X = g.gauss(A, R)
+        piv = g.pivots()
+    assert ol.max_rel_error(X, Xo) <= TOL
+    assert ol.scaled_residual(A, R, X) <= 10.0
+    # the same rows are chosen as by the reference's getPivot (:127-131): replay the oracle and compare
+    Ad, Rd = A.copy(), R.copy()
+    perm = np.empty(n, np.int32)
+    import ctypes as C
+    assert ol.oracle().oracle_compute_gauss_pivot(Ad.ctypes.data_as(ol._dp), Rd.ctypes.data_as(ol._dp),
+                                                  perm.ctypes.data_as(ol._ip), n, 2) == 0
+    assert np.array_equal(piv, perm)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_without_pivoting_the_same_system_fails_or_is_wrong(mode):
+    A, R, Xpre = permuted_system(300, 9)
+    try:
+        X = pkg.gauss(A, R, mode=mode)
+        assert ol.max_rel_error(X, Xpre) > TOL             # no-pivot elimination is unstable here
+    except pkg.SingularMatrix:
+        pass
+    X = pkg.gauss(A, R, mode=mode, pivoting=True)
+    assert ol.max_rel_error(X, Xpre) <= TOL
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("name", ["matrix_10", "jpwh_991", "orsreg_1"])
+def test_reference_matrices(external, name, mode):
+    A = ol.coo_to_dense(external, name)
+    R, Xpre = ol.init_rhs(A)
+    Xo = ol.gauss_pivot(A, R, nthreads=4)
+    X = pkg.gauss(A, R, mode=mode, pivoting=True)
+    # the reference's own metric (:246-253) against the preset solution; FP32 instead of double, so the
+    # bound is the north_star's 1e-3 rather than the reference's 1e-15 .. 1e-10
+    print(name, "Error (GPU, FP32):", ol.max_rel_error(X, Xpre), " reference (double):", float(external[f"{name}_ref_error"]))
+    assert ol.max_rel_error(X, Xpre) <= TOL
+    assert ol.max_rel_error(X, Xo) <= TOL
+    if name == "matrix_10":
+        assert ol.max_rel_error(X, Xpre) == 0.0            # the reference prints "Error: 0.000000e+00" for it
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_zero_column_is_singular(mode):
+    A, R, _ = permuted_system(200, 5)
+    A[:, 37] = 0.0
+    with pkg.GaussCuda(200, mode=mode) as g:
+        g.set_pivoting(True)
+        with pytest.raises(pkg.SingularMatrix):
+            g.gauss(A, R)
+        assert g.stats.zero_pivot_row == 37
+
+
+def test_external_harness_cli(external, tmp_path):
+    exe = os.path.join(ROOT, "harness", "gauss_external_main")
+    if not os.path.exists(exe):
+        pytest.skip("harness not built")
+    path = tmp_path / "matrix_10.dat"
+    path.write_bytes(external["matrix_10_text"].tobytes())
+    out = subprocess.run([exe, str(path), "4"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert "Matrix Size: 10 ; Threads:" in out.stdout and "Time:" in out.stdout
+    assert "Error: 0.000000e+00" in out.stdout              # what the reference prints for this file
+    out = subprocess.run([exe, str(tmp_path / "nope.dat")], capture_output=True, text=True)
+    assert out.returncode != 0 and "The matrix file open error" in out.stderr
