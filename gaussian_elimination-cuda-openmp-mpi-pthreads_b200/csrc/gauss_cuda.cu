@@ -137,6 +137,14 @@ struct gauss_cuda_ctx {
     float* hvec = nullptr;   // [np] staging for RHS upload / B_out
     int* status = nullptr;   // device: 0 or (row+1) of the first bad pivot
     int* trsv_ctrl = nullptr;   // device: ticket + per-128-block flags of the fused back substitution
+    int* sched = nullptr;       // device: this context's tile-scheduler slots for the TC GEMM (2 x 64 ints)
+    // the whole elimination + back substitution of a single-GPU context is a fixed launch sequence:
+    // it is captured once into a CUDA graph and replayed, which takes the host out of the loop
+    // (at N = 2048 the ~90 launches otherwise cost more host time than the GPU needs to run them)
+    cudaGraphExec_t gexec = nullptr;
+    bool capturing = false, graph_failed = false, use_graph = true;
+    long long graph_launches = 0;
+    int graph_upd_count = 0;
     bool pivot = false;         // partial pivoting (external-input variant)
     float* pt = nullptr;        // packed panel scratch [128 x np]
     int* ipiv = nullptr;        // device: pivot row of every step
@@ -183,6 +191,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     }
     gauss_cuda_ctx* c = new gauss_cuda_ctx();
     c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode;
+    { const char* g = getenv("GAUSS_CUDA_GRAPH"); if (g && atoi(g) == 0) c->use_graph = false; }
     c->np = round_up(n, kNb);
     c->ld = c->np + kPadCols;
     if (nb == 0) {
@@ -205,6 +214,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     A((void**)&c->hvec, (size_t)c->np * sizeof(float));
     A((void**)&c->status, sizeof(int));
     A((void**)&c->trsv_ctrl, (size_t)(c->np / kNb + 1) * sizeof(int));
+    A((void**)&c->sched, 128 * sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(c->sched, 0, 128 * sizeof(int));
     if (world > 1) for (int i = 0; i < 2; ++i) A((void**)&c->pbuf[i], (size_t)c->NB * c->ld * sizeof(float));
     if (mode == GAUSS_CUDA_MODE_3XTF32) {
         const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
@@ -272,7 +283,9 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi, c->la_lo, c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
     if (c->status) cudaFree(c->status);
+    if (c->gexec) cudaGraphExecDestroy(c->gexec);
     if (c->trsv_ctrl) cudaFree(c->trsv_ctrl);
+    if (c->sched) cudaFree(c->sched);
     if (c->pt) cudaFree(c->pt);
     if (c->ipiv) cudaFree(c->ipiv);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
@@ -326,9 +339,17 @@ static int gemm_update(gauss_cuda_ctx* c, const float* A, int lda, const float* 
         launch_sgemm_nn(A, lda, B, ldb, C, c->ld, m, ncols, k, -1.f, 1.f, c->s_main);
         return GAUSS_CUDA_OK;
     }
+    tc_set_sched_slots(c->sched);
     int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, c->s_main);
+    tc_set_sched_slots(nullptr);
     if (rc) return cuda_fail((cudaError_t)rc, "tc_gemm_nt", __LINE__);
     return GAUSS_CUDA_OK;
+}
+
+// Event record that stays usable for cudaEventElapsedTime when the stream is being captured.
+static cudaError_t rec_event(gauss_cuda_ctx* c, cudaEvent_t ev, cudaStream_t s)
+{
+    return c->capturing ? cudaEventRecordWithFlags(ev, s, cudaEventRecordExternal) : cudaEventRecord(ev, s);
 }
 
 // ---- the pieces of one outer step --------------------------------------------------------
@@ -425,14 +446,14 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row
     float* Wb = c->W + (size_t)row_lo * ld;
     const int ui = c->upd_count;
     const bool timed = (size_t)(2 * ui + 1) < c->upd_ev.size();
-    if (timed) CK(cudaEventRecord(c->upd_ev[2 * ui], s));
+    if (timed) CK(rec_event(c, c->upd_ev[2 * ui], s));
     int rc = gemm_update(c, Wb + k0, ld, pr.pu, pr.ldu,
                          tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr,
                          tc ? pr.ub_hi + (size_t)(k0 + kb) * NB : nullptr, tc ? pr.ub_lo + (size_t)(k0 + kb) * NB : nullptr,
                          Wb + k0 + kb, m, ld - (k0 + kb), kb);
     if (rc) return rc;
     if (timed) {
-        CK(cudaEventRecord(c->upd_ev[2 * ui + 1], s));
+        CK(rec_event(c, c->upd_ev[2 * ui + 1], s));
         c->upd_flops[ui] = 2.0 * (double)m * (double)(np + 1 - (k0 + kb)) * (double)kb;
         c->upd_count = ui + 1;
     }
@@ -660,6 +681,56 @@ static int snapshot_rhs(gauss_cuda_ctx* c)
     return GAUSS_CUDA_OK;
 }
 
+// ev[1] | computeGauss | ev[2] | snapshot of y | solveGauss | ev[3]
+static int core_body(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main;
+    int rc;
+    CK(rec_event(c, c->ev[1], s));
+    if ((rc = factor(c))) return rc;
+    CK(rec_event(c, c->ev[2], s));
+    if ((rc = snapshot_rhs(c))) return rc;
+    if ((rc = backsub(c))) return rc;
+    CK(rec_event(c, c->ev[3], s));
+    return GAUSS_CUDA_OK;
+}
+
+static int run_core(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main;
+    const bool graphable = c->world == 1 && !c->pivot && c->use_graph && !c->graph_failed;
+    if (graphable && !c->gexec) {
+        const long long before = g_launch_count;
+        c->capturing = true;
+        cudaError_t e = cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+        int rc = e == cudaSuccess ? core_body(c) : GAUSS_CUDA_CUDA_ERR;
+        cudaGraph_t graph = nullptr;
+        if (e == cudaSuccess) e = cudaStreamEndCapture(s, &graph);
+        c->capturing = false;
+        if (rc == GAUSS_CUDA_OK && e == cudaSuccess && graph) e = cudaGraphInstantiate(&c->gexec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (rc != GAUSS_CUDA_OK || e != cudaSuccess || !c->gexec) {
+            c->gexec = nullptr;
+            c->graph_failed = true;                      // fall back to plain launches for good
+            cudaGetLastError();
+        } else {
+            c->graph_launches = g_launch_count - before;
+            c->graph_upd_count = c->upd_count;
+        }
+        g_launch_count = before;
+    }
+    if (graphable && c->gexec) {
+        CK(cudaMemsetAsync(c->status, 0, sizeof(int), s));   // (also inside the graph; harmless)
+        c->upd_count = c->graph_upd_count;
+        c->bcast_bytes = 0.0;
+        CK(cudaGraphLaunch(c->gexec, s));
+        g_launch_count += c->graph_launches;
+        c->factored = true;
+        return GAUSS_CUDA_OK;
+    }
+    return core_body(c);
+}
+
 extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* B, float* X, float* B_out, gauss_cuda_stats* st)
 {
     if (!c || !A || !B || !X) return GAUSS_CUDA_BAD_ARG;
@@ -669,12 +740,7 @@ extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* 
     int rc;
     CK(cudaEventRecord(c->ev[0], s));
     if ((rc = upload_into(c, c->W, A, B))) return rc;
-    CK(cudaEventRecord(c->ev[1], s));
-    if ((rc = factor(c))) return rc;
-    CK(cudaEventRecord(c->ev[2], s));
-    if (B_out && (rc = snapshot_rhs(c))) return rc;
-    if ((rc = backsub(c))) return rc;
-    CK(cudaEventRecord(c->ev[3], s));
+    if ((rc = run_core(c))) return rc;
     if ((rc = download_results(c, X, B_out))) return rc;
     CK(cudaEventRecord(c->ev[4], s));
     return finish_stats(c, st, true, true, true, true);
@@ -709,12 +775,7 @@ extern "C" int gauss_cuda_solve_resident(gauss_cuda_ctx* c, gauss_cuda_stats* st
     int rc;
     CK(cudaEventRecord(c->ev[0], s));
     if ((rc = restore_working(c))) return rc;
-    CK(cudaEventRecord(c->ev[1], s));
-    if ((rc = factor(c))) return rc;
-    CK(cudaEventRecord(c->ev[2], s));
-    if ((rc = snapshot_rhs(c))) return rc;
-    if ((rc = backsub(c))) return rc;
-    CK(cudaEventRecord(c->ev[3], s));
+    if ((rc = run_core(c))) return rc;
     CK(cudaEventRecord(c->ev[4], s));
     return finish_stats(c, st, true, true, true, false);
 }

@@ -34,17 +34,11 @@ void launch_lcol(const float* u11, int ldu, float* a21, int ld, int nrows,
 void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C, int ldc,
                      int m, int n, int k, float alpha, float beta, cudaStream_t s);
 
-// Back substitution pieces (unit-upper U):
-//  trsv_diag:  x[0..128) = U_kk^-1 * y_k for the 128x128 diagonal block at `ukk`; y is read from
-//              column `ycol` of the same rows (ycol relative to ukk), x also written back there.
-//  trsv_gemv:  y[r] -= U[r, blk] . x  for `nrows` rows starting at `u` (ld), y at column offset ycol.
-void launch_trsv_diag(float* ukk, int ld, int ycol, float* x, cudaStream_t s);
 // Whole back substitution of an [nrows x nrows] unit-upper system in one launch: x = U^-1 * W[:, ycol]
 // (W points at the system's element (0,0); ycol is relative to it).  ctrl: nrows/128 + 1 ints of device
 // scratch (ticket + per-block flags), reset here.  W is not modified.
 void launch_trsv_fused(const float* W, int ld, int nrows, int ycol, float* x, int* ctrl, cudaStream_t s);
 void launch_trsv_gemv_wide(float* u, int ld, int ycol, const float* x, int nrows, int kw, cudaStream_t s);
-void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cudaStream_t s);
 
 // Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.
 void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s);
@@ -74,6 +68,9 @@ void launch_panel_pivot(float* W, int ld, int np, int k0, float* pt, int mp, int
 int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
                float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s);
 bool tc_available();
+// Scheduler slots (2 * 64 zeroed ints of device memory) used by this thread's following tc_gemm_nt calls;
+// nullptr = the library's own ring.
+void tc_set_sched_slots(int* slots);
 
 extern thread_local long long g_launch_count;   // kernels launched by this thread since last reset
 

@@ -137,83 +137,7 @@ void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C,
 }
 
 // =====================================================================================
-// 5. Back substitution (solveGauss :144-159), blocked by 128: a one-CTA solve of the
-//    diagonal block, then y[rows above] -= U[rows above, block] * x_block with float4
-//    row reads (each warp streams whole 512 B row segments).
-// =====================================================================================
-constexpr int kTrsvDiagSmem = (kNb * (kNb + 1) + kNb) * (int)sizeof(float);
-
-__global__ void __launch_bounds__(128)
-trsv_diag_kernel(float* __restrict__ ukk, int ld, int ycol, float* __restrict__ x)
-{
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float (*U)[kNb + 1] = reinterpret_cast<float (*)[kNb + 1]>(smem_raw);
-    float* xs = reinterpret_cast<float*>(smem_raw) + kNb * (kNb + 1);
-    const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
-    for (int r = wrp; r < kNb; r += 4) {
-        const float4 v = *reinterpret_cast<const float4*>(ukk + (size_t)r * ld + 4 * lane);
-        U[r][4 * lane] = v.x; U[r][4 * lane + 1] = v.y; U[r][4 * lane + 2] = v.z; U[r][4 * lane + 3] = v.w;
-    }
-    float y = ukk[(size_t)tid * ld + ycol];       // thread t owns row t of the block
-    __syncthreads();
-    for (int b = 3; b >= 0; --b) {
-        if (wrp == b) {                           // 32x32 triangle: one warp, shuffles only
-            for (int i = 31; i >= 0; --i) {
-                const float xi = __shfl_sync(0xffffffffu, y, i);
-                if (lane < i) y = fmaf(-U[32 * b + lane][32 * b + i], xi, y);
-            }
-            xs[tid] = y;
-        }
-        __syncthreads();
-        if (wrp < b) {                            // rows above: subtract this sub-block's contribution
-#pragma unroll 8
-            for (int i = 0; i < 32; ++i) y = fmaf(-U[tid][32 * b + i], xs[32 * b + i], y);
-        }
-    }
-    x[tid] = y;
-    ukk[(size_t)tid * ld + ycol] = y;
-}
-
-__global__ void __launch_bounds__(256)
-trsv_gemv_kernel(float* __restrict__ u, int ld, int ycol, const float* __restrict__ x, int nrows)
-{
-    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    const float4 xv = *reinterpret_cast<const float4*>(x + 4 * lane);
-    const int r0 = (blockIdx.x * 8 + wrp) * 4;             // 4 rows per warp, 32 rows per CTA
-    float s[4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        s[i] = 0.f;
-        if (r0 + i < nrows) {
-            const float4 v = *reinterpret_cast<const float4*>(u + (size_t)(r0 + i) * ld + 4 * lane);
-            s[i] = v.x * xv.x + v.y * xv.y + v.z * xv.z + v.w * xv.w;
-        }
-    }
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) s[i] += __shfl_xor_sync(0xffffffffu, s[i], off);
-    if (lane < 4 && r0 + lane < nrows) {
-        const float mine = lane == 0 ? s[0] : lane == 1 ? s[1] : lane == 2 ? s[2] : s[3];
-        float* yp = u + (size_t)(r0 + lane) * ld + ycol;
-        *yp -= mine;
-    }
-}
-
-void launch_trsv_diag(float* ukk, int ld, int ycol, float* x, cudaStream_t s)
-{
-    trsv_diag_kernel<<<1, 128, kTrsvDiagSmem, s>>>(ukk, ld, ycol, x);
-    ++g_launch_count;
-}
-void launch_trsv_gemv(float* u, int ld, int ycol, const float* x, int nrows, cudaStream_t s)
-{
-    if (nrows <= 0) return;
-    trsv_gemv_kernel<<<(nrows + 31) / 32, 256, 0, s>>>(u, ld, ycol, x, nrows);
-    ++g_launch_count;
-}
-
-// =====================================================================================
-// 5b. Back substitution in ONE launch (single-GPU path).  CTAs take 128-row blocks bottom-up through
+// 5. Back substitution (solveGauss :144-159) in ONE launch.  CTAs take 128-row blocks bottom-up through
 //     an atomic ticket (so a CTA only ever waits for CTAs that already run), stream their rows of U
 //     with float4 loads while folding in x_J as the blocks below publish it (per-block flags,
 //     release/acquire), then solve their own diagonal block with the inverses of its four 32x32
@@ -491,7 +415,6 @@ void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int
 void simt_setup_device()
 {
     panel_setup_device();
-    cudaFuncSetAttribute(trsv_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTrsvDiagSmem);
     cudaFuncSetAttribute(trsv_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TrsvSmem));
 }
 

@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant__ CUtensorMap tm_alo,
                const __grid_constant__ CUtensorMap tm_bhi, const __grid_constant__ CUtensorMap tm_blo,
                const __grid_constant__ CUtensorMap tm_c,
-               int m, int n, int k, int negate, int reduce, int* __restrict__ sched)
+               int m, int n, int k, int negate, int reduce, int* __restrict__ sched, int dynamic)
 {
     using Cfg = TcCfg<BK, STAGES>;
     extern __shared__ unsigned char smem_dyn[];
@@ -218,7 +218,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
             // gets its SM late (or shares the GPU with another stream's kernels) simply takes fewer tiles
             for (int it = 0;; ++it) {
                 const int q = it & 3;
-                int t = it == 0 ? (int)blockIdx.x : atomicAdd(sched, 1) + (int)gridDim.x;
+                int t = (it == 0 || !dynamic) ? (int)blockIdx.x + it * (int)gridDim.x : atomicAdd(sched, 1) + (int)gridDim.x;
                 if (t >= num_tiles) t = -1;
                 mbar_wait(qempty_bar(q), ((it >> 2) & 1) ^ 1);
                 q_tile[q] = t;
@@ -333,7 +333,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
     }
     // the last CTA to leave rearms the scheduler slot for a later launch (sched[0] tile counter, sched[1] exits)
-    if (threadIdx.x == 0) {
+    if (dynamic && threadIdx.x == 0) {
         __threadfence();
         if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) { sched[0] = 0; sched[1] = 0; __threadfence(); }
     }
@@ -353,6 +353,10 @@ constexpr int kSchedSlots = 64;
 static __device__ int g_sched_slots[2 * kSchedSlots];
 static int* g_sched_addr[16] = {nullptr};
 static unsigned g_sched_next = 0;
+// Callers that replay their launches from a CUDA graph own their scheduler slots (so two graphs running
+// on different streams can never share one); everyone else uses the library's ring.
+static thread_local int* t_sched_override = nullptr;
+static int g_dynamic = 1;            // GAUSS_CUDA_TC_STATIC=1 falls back to static round-robin tiles
 static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
 
 bool tc_available()
@@ -373,6 +377,8 @@ int tc_setup_device()
     }
     const char* v = getenv("GAUSS_CUDA_TC_VARIANT");
     if (v) g_variant = atoi(v) ? 1 : 0;
+    const char* st = getenv("GAUSS_CUDA_TC_STATIC");
+    g_dynamic = (st && atoi(st)) ? 0 : 1;
     const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
     if (rs) g_reserve_sms = atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs));
     int dev = 0;
@@ -421,11 +427,14 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
-    int* sched = g_sched_addr[dev] + 2 * (g_sched_next++ % kSchedSlots);
-    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched);
+    int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
+    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched,
+                                                                 (g_dynamic && tiles > grid) ? 1 : 0);
     ++g_launch_count;
     return (int)cudaGetLastError();
 }
+
+void tc_set_sched_slots(int* slots) { t_sched_override = slots; }
 
 int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
                float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
