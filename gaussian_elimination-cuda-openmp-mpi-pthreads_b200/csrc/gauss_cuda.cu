@@ -130,7 +130,12 @@ struct gauss_cuda_ctx {
     float* W = nullptr;      // working augmented matrix  [rows_local x ld]
     float* W0 = nullptr;     // resident pristine copy (gauss_cuda_upload), same shape
     float* pbuf[2] = {nullptr, nullptr};   // packed row panels [NB x ld], double buffered   (world > 1)
-    float* la_hi = nullptr, *la_lo = nullptr;   // [rows_local x NB]  split L operand (3xTF32 mode)
+    float* la_hi[2] = {nullptr, nullptr};       // [rows_local x NB]  split L operand (3xTF32 mode);
+    float* la_lo[2] = {nullptr, nullptr};       //                    second copy for the single-GPU look-ahead
+    cudaStream_t s_panel = nullptr;             // higher-priority stream of the single-GPU look-ahead
+    cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
+    bool overlap = false;
+    int overlap_max_tiles = 6;
     float* ub_hi[2] = {nullptr, nullptr};       // [ld x NB]          split U operand, transposed;
     float* ub_lo[2] = {nullptr, nullptr};       //                    second copy only when world > 1 (look-ahead)
     float* xvec = nullptr;   // [np] solution
@@ -192,6 +197,14 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     gauss_cuda_ctx* c = new gauss_cuda_ctx();
     c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode;
     { const char* g = getenv("GAUSS_CUDA_GRAPH"); if (g && atoi(g) == 0) c->use_graph = false; }
+    {   // single-GPU look-ahead (GAUSS_CUDA_OVERLAP=1): measured on B200 it is a wash -- the urow/lcol kernels are
+        // throughput-bound, so running them beside the bulk update only moves SM time around (N=32768: 132.0 ms
+        // with, 128.7 ms without) -- and it is therefore off unless asked for
+        const char* o = getenv("GAUSS_CUDA_OVERLAP");
+        c->overlap = world == 1 && o && atoi(o) != 0;
+        const char* mt = getenv("GAUSS_CUDA_OVERLAP_TILES");
+        if (mt && atoi(mt) > 0) c->overlap_max_tiles = atoi(mt);
+    }
     c->np = round_up(n, kNb);
     c->ld = c->np + kPadCols;
     if (nb == 0) {
@@ -220,14 +233,24 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     if (mode == GAUSS_CUDA_MODE_3XTF32) {
         const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
         const size_t ub = (size_t)c->ld * c->NB * sizeof(float);
-        A((void**)&c->la_hi, la); A((void**)&c->la_lo, la);
-        for (int i = 0; i < (world > 1 ? 2 : 1); ++i) {
+        A((void**)&c->la_hi[0], la); A((void**)&c->la_lo[0], la);
+        if (c->overlap) { A((void**)&c->la_hi[1], la); A((void**)&c->la_lo[1], la); }
+        for (int i = 0; i < ((world > 1 || c->overlap) ? 2 : 1); ++i) {
             A((void**)&c->ub_hi[i], ub); A((void**)&c->ub_lo[i], ub);
             if (e == cudaSuccess) e = cudaMemset(c->ub_hi[i], 0, ub);
             if (e == cudaSuccess) e = cudaMemset(c->ub_lo[i], 0, ub);
         }
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
+    if (c->overlap) {
+        int lo_p = 0, hi_p = 0;
+        cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p);
+        if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->s_panel, cudaStreamNonBlocking, hi_p);
+        for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+            e = cudaEventCreateWithFlags(&c->ev_fork[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
+        }
+    }
     if (world > 1) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_comm, cudaStreamNonBlocking);
         for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
@@ -238,8 +261,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         }
     }
     for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
-    c->upd_ev.assign(4 * (size_t)c->nblk, nullptr);            // look-ahead splits some updates in two launches
-    c->upd_flops.assign(2 * (size_t)c->nblk, 0.0);
+    c->upd_ev.assign(6 * (size_t)c->nblk, nullptr);            // look-ahead splits the update in up to three launches
+    c->upd_flops.assign(3 * (size_t)c->nblk, 0.0);
     for (size_t i = 0; i < c->upd_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->upd_ev[i]);
     if (e != cudaSuccess) { int rc = cuda_fail(e, "context allocation", __LINE__); gauss_cuda_free(c); return rc; }
 
@@ -280,7 +303,9 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     if (c->s_main) cudaStreamSynchronize(c->s_main);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     if (c->s_comm) cudaStreamSynchronize(c->s_comm);
-    float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi, c->la_lo, c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
+    if (c->s_panel) cudaStreamSynchronize(c->s_panel);
+    float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi[0], c->la_lo[0], c->la_hi[1], c->la_lo[1],
+                     c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
     if (c->status) cudaFree(c->status);
     if (c->gexec) cudaGraphExecDestroy(c->gexec);
@@ -297,6 +322,11 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
         if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
     }
     if (c->s_comm) cudaStreamDestroy(c->s_comm);
+    for (int i = 0; i < 2; ++i) {
+        if (c->ev_fork[i]) cudaEventDestroy(c->ev_fork[i]);
+        if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
+    }
+    if (c->s_panel) cudaStreamDestroy(c->s_panel);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     delete c;
 }
@@ -330,17 +360,19 @@ static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const floa
 // ------------------------------------------------------------------------------------------
 // elimination
 // ------------------------------------------------------------------------------------------
-static int gemm_update(gauss_cuda_ctx* c, const float* A, int lda, const float* B, int ldb,
+static int gemm_update(gauss_cuda_ctx* c, cudaStream_t s, const float* A, int lda, const float* B, int ldb,
                        const float* Ahi, const float* Alo, const float* Bhi, const float* Blo,
-                       float* C, int m, int ncols, int k)
+                       float* C, int m, int ncols, int k, int max_tiles = 0)
 {
     if (m <= 0 || ncols <= 0) return GAUSS_CUDA_OK;
     if (c->mode == GAUSS_CUDA_MODE_FFMA) {
-        launch_sgemm_nn(A, lda, B, ldb, C, c->ld, m, ncols, k, -1.f, 1.f, c->s_main);
+        launch_sgemm_nn(A, lda, B, ldb, C, c->ld, m, ncols, k, -1.f, 1.f, s);
         return GAUSS_CUDA_OK;
     }
     tc_set_sched_slots(c->sched);
-    int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, c->s_main);
+    tc_set_max_tiles(max_tiles);
+    int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, s);
+    tc_set_max_tiles(0);
     tc_set_sched_slots(nullptr);
     if (rc) return cuda_fail((cudaError_t)rc, "tc_gemm_nt", __LINE__);
     return GAUSS_CUDA_OK;
@@ -358,11 +390,15 @@ struct PanelRef {            // where the factored row panel of the current oute
     const float* pu; int ldu;       // the U12 region:      element (panel row 0, column k0 + kb)
     float* ub_hi; float* ub_lo;     // split, transposed U operand of this step (3xTF32 mode)
 };
+struct StepBufs {            // the stream a piece runs on and the split-L buffers it reads / writes
+    cudaStream_t s;
+    float* la_hi; float* la_lo;
+};
 
 // P1: factor the row panel of outer block K in place on its owner.
-static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo)
+static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo, const StepBufs& sb)
 {
-    cudaStream_t s = c->s_main;
+    cudaStream_t s = sb.s;
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
@@ -376,9 +412,9 @@ static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo)
         const int mrem = kb - (r + kNb);
         if (mrem > 0) {
             launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
-                        tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB : nullptr, NB, r, s);
-            int rc = gemm_update(c, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
-                                 tc ? c->la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? c->la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
+                        tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB : nullptr, NB, r, s);
+            int rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                                 tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
                                  tc ? ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
                                  P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
             if (rc) return rc;
@@ -409,9 +445,9 @@ static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr, bool d
 }
 
 // P2: L-col solves and in-panel updates for the local rows [row_lo, rows_local).
-static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo)
+static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo, const StepBufs& sb)
 {
-    cudaStream_t s = c->s_main;
+    cudaStream_t s = sb.s;
     const int ld = c->ld, NB = c->NB;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
@@ -421,11 +457,11 @@ static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo)
     for (int j = 0; j < ninner; ++j) {
         const int kk = k0 + j * kNb, r = j * kNb;
         launch_lcol(pr.pd + (size_t)r * pr.ldd + r, pr.ldd, Wb + kk, ld, m,
-                    tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr, NB, r, s);
+                    tc ? sb.la_hi + (size_t)row_lo * NB : nullptr, tc ? sb.la_lo + (size_t)row_lo * NB : nullptr, NB, r, s);
         const int nin = kb - (r + kNb);                    // columns of the panel still to the right
         if (nin > 0) {
-            int rc = gemm_update(c, Wb + kk, ld, pr.pd + (size_t)r * pr.ldd + r + kNb, pr.ldd,
-                                 tc ? c->la_hi + (size_t)row_lo * NB + r : nullptr, tc ? c->la_lo + (size_t)row_lo * NB + r : nullptr,
+            int rc = gemm_update(c, s, Wb + kk, ld, pr.pd + (size_t)r * pr.ldd + r + kNb, pr.ldd,
+                                 tc ? sb.la_hi + (size_t)row_lo * NB + r : nullptr, tc ? sb.la_lo + (size_t)row_lo * NB + r : nullptr,
                                  tc ? pr.ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? pr.ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
                                  Wb + kk + kNb, m, nin, kNb);
             if (rc) return rc;
@@ -434,44 +470,97 @@ static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo)
     return GAUSS_CUDA_OK;
 }
 
-// P3: A22 -= L21 * U12 for the local rows [row_lo, row_hi), all columns right of the panel.  Timed.
-static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo, int row_hi)
+// P3: A22 -= L21 * U12 for the local rows [row_lo, row_hi) and the columns [col_lo, col_lo + ncols) right of the
+// panel (ncols < 0: all of them).  Timed.  max_tiles > 0 bounds how many tiles a CTA of the tile engine takes
+// before it exits, so that kernels of the (higher-priority) panel stream get SMs while this launch runs.
+static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const StepBufs& sb, int row_lo, int row_hi,
+                           int col_lo = -1, int ncols = -1, int max_tiles = 0)
 {
-    cudaStream_t s = c->s_main;
+    cudaStream_t s = sb.s;
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     const int k0 = K * NB, kb = blk_rows(c, K);
+    if (col_lo < 0) col_lo = k0 + kb;
+    if (ncols < 0) ncols = ld - col_lo;
     const int m = row_hi - row_lo;
-    if (m <= 0 || ld - (k0 + kb) <= 0) return GAUSS_CUDA_OK;
+    if (m <= 0 || ncols <= 0) return GAUSS_CUDA_OK;
     float* Wb = c->W + (size_t)row_lo * ld;
     const int ui = c->upd_count;
     const bool timed = (size_t)(2 * ui + 1) < c->upd_ev.size();
     if (timed) CK(rec_event(c, c->upd_ev[2 * ui], s));
-    int rc = gemm_update(c, Wb + k0, ld, pr.pu, pr.ldu,
-                         tc ? c->la_hi + (size_t)row_lo * NB : nullptr, tc ? c->la_lo + (size_t)row_lo * NB : nullptr,
-                         tc ? pr.ub_hi + (size_t)(k0 + kb) * NB : nullptr, tc ? pr.ub_lo + (size_t)(k0 + kb) * NB : nullptr,
-                         Wb + k0 + kb, m, ld - (k0 + kb), kb);
+    int rc = gemm_update(c, s, Wb + k0, ld, pr.pu + (col_lo - (k0 + kb)), pr.ldu,
+                         tc ? sb.la_hi + (size_t)row_lo * NB : nullptr, tc ? sb.la_lo + (size_t)row_lo * NB : nullptr,
+                         tc ? pr.ub_hi + (size_t)col_lo * NB : nullptr, tc ? pr.ub_lo + (size_t)col_lo * NB : nullptr,
+                         Wb + col_lo, m, ncols, kb, max_tiles);
     if (rc) return rc;
     if (timed) {
         CK(rec_event(c, c->upd_ev[2 * ui + 1], s));
-        c->upd_flops[ui] = 2.0 * (double)m * (double)(np + 1 - (k0 + kb)) * (double)kb;
+        const int real_cols = std::min(col_lo + ncols, np + 1) - col_lo;          // the zero padding is not credited
+        c->upd_flops[ui] = 2.0 * (double)m * (double)std::max(real_cols, 0) * (double)kb;
         c->upd_count = ui + 1;
     }
     return GAUSS_CUDA_OK;
 }
 
-// Single GPU: P1 -> P2 -> P3 per outer block, one stream.
+// Single GPU, one stream: P1 -> P2 -> P3 per outer block.
 static int factor_single(gauss_cuda_ctx* c)
 {
     const int ld = c->ld, NB = c->NB;
+    const StepBufs sb{c->s_main, c->la_hi[0], c->la_lo[0]};
     for (int K = 0; K < c->nblk; ++K) {
-        int rc = panel_factor(c, K, c->ub_hi[0], c->ub_lo[0]);
+        int rc = panel_factor(c, K, c->ub_hi[0], c->ub_lo[0], sb);
         if (rc) return rc;
         const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + K * NB;
         PanelRef pr{P0, ld, P0 + blk_rows(c, K), ld, c->ub_hi[0], c->ub_lo[0]};
         const int l0 = first_local_block_after(c, K) * NB;
-        if ((rc = col_panel(c, K, pr, l0))) return rc;
-        if ((rc = trailing_update(c, K, pr, l0, c->rows_local))) return rc;
+        if ((rc = col_panel(c, K, pr, l0, sb))) return rc;
+        if ((rc = trailing_update(c, K, pr, sb, l0, c->rows_local))) return rc;
+    }
+    return GAUSS_CUDA_OK;
+}
+
+// Single GPU with look-ahead on a second, higher-priority stream.  Step K first updates the strips the next
+// panel needs (the rows of block K+1, then the columns of block K+1 for the rows below), forks the whole panel
+// path of block K+1 (P1 + P2) onto the panel stream, and runs the bulk of the trailing update beside it; the
+// tile engine's CTAs give up their SM after a few tiles so the small, latency-bound panel kernels get in.
+// L21 and U12 splits are double buffered by the parity of K (the panel path writes the next step's while the
+// bulk update still reads this step's).
+static int factor_overlap(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main, sp = c->s_panel;
+    const int ld = c->ld, NB = c->NB;
+    int rc;
+    {   // block 0: nothing to overlap with
+        const StepBufs sb0{s, c->la_hi[0], c->la_lo[0]};
+        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sb0))) return rc;
+        const float* P0 = c->W;
+        PanelRef pr0{P0, ld, P0 + blk_rows(c, 0), ld, c->ub_hi[0], c->ub_lo[0]};
+        if ((rc = col_panel(c, 0, pr0, NB, sb0))) return rc;
+    }
+    for (int K = 0; K < c->nblk; ++K) {
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
+        const StepBufs sb{s, c->la_hi[b], c->la_lo[b]};
+        const float* P0 = c->W + (size_t)k0 * ld + k0;
+        PanelRef pr{P0, ld, P0 + kb, ld, c->ub_hi[b], c->ub_lo[b]};
+        const int l0 = k0 + kb;                                   // first row below the panel
+        if (K + 1 >= c->nblk) break;                              // the last block has no rows below it
+        const int rows_next = blk_rows(c, K + 1);
+        const int l1 = l0 + rows_next;                            // first row below block K+1
+        // strips the next panel depends on
+        if ((rc = trailing_update(c, K, pr, sb, l0, l1))) return rc;                          // rows of block K+1, all columns
+        if ((rc = trailing_update(c, K, pr, sb, l1, c->rows_local, l0, rows_next))) return rc; // rows below, columns of block K+1
+        CK(cudaEventRecord(c->ev_fork[b], s));
+        // panel path of block K+1 on the panel stream
+        CK(cudaStreamWaitEvent(sp, c->ev_fork[b], 0));
+        const StepBufs sbn{sp, c->la_hi[b ^ 1], c->la_lo[b ^ 1]};
+        if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbn))) return rc;
+        const float* P1 = c->W + (size_t)l0 * ld + l0;
+        PanelRef prn{P1, ld, P1 + rows_next, ld, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1]};
+        if ((rc = col_panel(c, K + 1, prn, l1, sbn))) return rc;
+        CK(cudaEventRecord(c->ev_join[b], sp));
+        // the bulk of the update, beside it
+        if ((rc = trailing_update(c, K, pr, sb, l1, c->rows_local, l1, -1, c->overlap_max_tiles))) return rc;
+        CK(cudaStreamWaitEvent(s, c->ev_join[b], 0));
     }
     return GAUSS_CUDA_OK;
 }
@@ -512,8 +601,9 @@ static int factor_lookahead(gauss_cuda_ctx* c)
     // both panel buffers start out free
     CK(cudaEventRecord(c->ev_free[0], s));
     CK(cudaEventRecord(c->ev_free[1], s));
+    const StepBufs sbm{s, c->la_hi[0], c->la_lo[0]};
     if (owner_of(0) == c->rank) {
-        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0]))) return rc;
+        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sbm))) return rc;
         CK(cudaEventRecord(c->ev_ready[0], s));
     }
     if ((rc = enqueue_bcast(0))) return rc;
@@ -531,7 +621,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
             if (tc) rebuild_split_u(c, K, pr, true);
         }
         const int l0 = first_local_block_after(c, K) * NB;
-        if ((rc = col_panel(c, K, pr, l0))) return rc;
+        if ((rc = col_panel(c, K, pr, l0, sbm))) return rc;
         if (!mine) {
             CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // ... and now the U12 region
             if (tc) rebuild_split_u(c, K, pr, false);
@@ -541,14 +631,14 @@ static int factor_lookahead(gauss_cuda_ctx* c)
             if (owner_of(K + 1) == c->rank) {
                 // block K+1 is this rank's first block below the panel: bring it up to date, factor it
                 const int rows_next = blk_rows(c, K + 1);
-                if ((rc = trailing_update(c, K, pr, l0, l0 + rows_next))) return rc;
-                if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1]))) return rc;
+                if ((rc = trailing_update(c, K, pr, sbm, l0, l0 + rows_next))) return rc;
+                if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbm))) return rc;
                 CK(cudaEventRecord(c->ev_ready[b ^ 1], s));
                 rest_lo = l0 + rows_next;
             }
             if ((rc = enqueue_bcast(K + 1))) return rc;
         }
-        if ((rc = trailing_update(c, K, pr, rest_lo, c->rows_local))) return rc;
+        if ((rc = trailing_update(c, K, pr, sbm, rest_lo, c->rows_local))) return rc;
         CK(cudaEventRecord(c->ev_free[b], s));                    // pbuf[b] / ub[b] may be overwritten from here on
     }
     CK(cudaEventRecord(c->ev_done[0], sc));
@@ -567,15 +657,15 @@ static int factor_pivot(gauss_cuda_ctx* c)
     for (int k0 = 0; k0 < np; k0 += kNb) {
         const int below = k0 + kNb;
         launch_panel_pivot(c->W, ld, np, k0, c->pt, np, c->ipiv, c->status,
-                           tc ? c->la_hi + (size_t)below * NB : nullptr, tc ? c->la_lo + (size_t)below * NB : nullptr, NB, s);
+                           tc ? c->la_hi[0] + (size_t)below * NB : nullptr, tc ? c->la_lo[0] + (size_t)below * NB : nullptr, NB, s);
         float* P = c->W + (size_t)k0 * ld;
         launch_urow(P + k0, ld, P + below, ld, np + 1 - below,
                     tc ? c->ub_hi[0] + (size_t)below * NB : nullptr, tc ? c->ub_lo[0] + (size_t)below * NB : nullptr, NB, 0, s);
         const int m = np - below;
         if (m > 0) {
             float* Wb = c->W + (size_t)below * ld;
-            int rc = gemm_update(c, Wb + k0, ld, P + below, ld,
-                                 tc ? c->la_hi + (size_t)below * NB : nullptr, tc ? c->la_lo + (size_t)below * NB : nullptr,
+            int rc = gemm_update(c, s, Wb + k0, ld, P + below, ld,
+                                 tc ? c->la_hi[0] + (size_t)below * NB : nullptr, tc ? c->la_lo[0] + (size_t)below * NB : nullptr,
                                  tc ? c->ub_hi[0] + (size_t)below * NB : nullptr, tc ? c->ub_lo[0] + (size_t)below * NB : nullptr,
                                  Wb + below, m, ld - below, kNb);
             if (rc) return rc;
@@ -589,7 +679,9 @@ static int factor(gauss_cuda_ctx* c)
     CK(cudaMemsetAsync(c->status, 0, sizeof(int), c->s_main));
     c->bcast_bytes = 0.0;
     c->upd_count = 0;
-    int rc = c->pivot ? factor_pivot(c) : (c->world > 1 ? factor_lookahead(c) : factor_single(c));
+    int rc = c->pivot ? factor_pivot(c)
+           : c->world > 1 ? factor_lookahead(c)
+           : (c->overlap && c->nblk >= 3) ? factor_overlap(c) : factor_single(c);
     if (rc) return rc;
     CK(cudaGetLastError());
     c->factored = true;

@@ -71,6 +71,9 @@ bool tc_available();
 // Scheduler slots (2 * 64 zeroed ints of device memory) used by this thread's following tc_gemm_nt calls;
 // nullptr = the library's own ring.
 void tc_set_sched_slots(int* slots);
+// > 0: CTAs of this thread's following tc_gemm_nt launches exit after that many tiles (the grid grows to match),
+// so kernels of other streams get SMs while a long launch runs.  0 = persistent CTAs.
+void tc_set_max_tiles(int max_tiles);
 
 extern thread_local long long g_launch_count;   // kernels launched by this thread since last reset
 

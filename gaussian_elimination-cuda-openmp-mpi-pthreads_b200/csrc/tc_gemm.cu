@@ -172,7 +172,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant__ CUtensorMap tm_alo,
                const __grid_constant__ CUtensorMap tm_bhi, const __grid_constant__ CUtensorMap tm_blo,
                const __grid_constant__ CUtensorMap tm_c,
-               int m, int n, int k, int negate, int reduce, int* __restrict__ sched, int dynamic)
+               int m, int n, int k, int negate, int reduce, int* __restrict__ sched, int dynamic, int max_tiles)
 {
     using Cfg = TcCfg<BK, STAGES>;
     extern __shared__ unsigned char smem_dyn[];
@@ -218,7 +218,13 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
             // gets its SM late (or shares the GPU with another stream's kernels) simply takes fewer tiles
             for (int it = 0;; ++it) {
                 const int q = it & 3;
-                int t = (it == 0 || !dynamic) ? (int)blockIdx.x + it * (int)gridDim.x : atomicAdd(sched, 1) + (int)gridDim.x;
+                // dynamic == 1: first tile static, the rest from the counter; dynamic == 2 (bounded CTAs, grid larger
+                // than the SM count): every tile from the counter so the tile order stays the band order
+                int t;
+                if (max_tiles > 0 && it >= max_tiles) t = -1;                       // this CTA has had its share
+                else if (dynamic == 2) t = atomicAdd(sched, 1);
+                else if (it == 0 || !dynamic) t = (int)blockIdx.x + it * (int)gridDim.x;
+                else t = atomicAdd(sched, 1) + (int)gridDim.x;
                 if (t >= num_tiles) t = -1;
                 mbar_wait(qempty_bar(q), ((it >> 2) & 1) ^ 1);
                 q_tile[q] = t;
@@ -356,6 +362,7 @@ static unsigned g_sched_next = 0;
 // Callers that replay their launches from a CUDA graph own their scheduler slots (so two graphs running
 // on different streams can never share one); everyone else uses the library's ring.
 static thread_local int* t_sched_override = nullptr;
+static thread_local int t_max_tiles = 0;
 static int g_dynamic = 1;            // GAUSS_CUDA_TC_STATIC=1 falls back to static round-robin tiles
 static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
 
@@ -423,18 +430,25 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     if (rc) return (int)cudaErrorInvalidValue;
     const int tiles = ((m + TBM - 1) / TBM) * ((n + TBN - 1) / TBN);
     const int avail = g_num_sms - g_reserve_sms;
-    const int grid = tiles < avail ? tiles : avail;
+    int grid = tiles < avail ? tiles : avail;
+    int dyn = (g_dynamic && tiles > grid) ? 1 : 0;
+    int max_tiles = 0;
+    if (t_max_tiles > 0 && g_dynamic && tiles > avail * t_max_tiles / 2) {     // bounded CTAs: only worth it for big launches
+        max_tiles = t_max_tiles;
+        grid = (tiles + max_tiles - 1) / max_tiles;
+        dyn = 2;
+    }
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
     int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
-    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched,
-                                                                 (g_dynamic && tiles > grid) ? 1 : 0);
+    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched, dyn, max_tiles);
     ++g_launch_count;
     return (int)cudaGetLastError();
 }
 
 void tc_set_sched_slots(int* slots) { t_sched_override = slots; }
+void tc_set_max_tiles(int max_tiles) { t_max_tiles = max_tiles; }
 
 int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
                float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
