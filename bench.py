@@ -425,6 +425,17 @@ def bench_matmul(args, pkg, n, mode, peaks, peak_src, cores, rank):
             ref_ms = ol.ref_matmul().ref_gpu_matmul(dA.data_ptr(), dB.data_ptr(), dR.data_ptr(), n)
     except OSError:
         pass
+    cpu = None
+    if not args.no_cpu_baseline:
+        try:                                 # the reference's own OpenMP loop (cuda_matmul.cu:42-57) on the host cores
+            import oracle_lib as ol
+            t0 = time.perf_counter()
+            ol.ref_cpu_matmul(A, B, omp=True)
+            tc = time.perf_counter() - t0
+            cpu = {"value": flop / tc * 1e-9, "unit": UNIT, "cores": cores, "kind": "reference",
+                   "sample": f"omp_matmul at N={n} (the full workload), one run, {tc:.2f} s"}
+        except OSError:
+            cpu = None
     tf32x3 = peaks["bf16_tflops_sustained"] / 6.0
     line = {"metric": "matmul_gflops", "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -435,7 +446,7 @@ def bench_matmul(args, pkg, n, mode, peaks, peak_src, cores, rank):
                     "ms_per_step": e2e_s * 1e3, "note": "matmul_cuda: cudaMalloc + 2 H2D + kernels + D2H + cudaFree, pageable host memory, like cuda_matmul.cu:135-165"},
             "roofline": {"bound": "tensor", "achieved": value * 1e-3, "peak": tf32x3, "unit": "TFLOP/s", "frac": value * 1e-3 / tf32x3,
                          "traffic": None, "peak_basis": f"{peak_src} bf16_tflops_sustained / 6", "note": "includes the two operand split/transposes"},
-            "reference_kernel_ms_on_this_gpu": ref_ms, "clocks": clocks}
+            "reference_kernel_ms_on_this_gpu": ref_ms, "cpu_baseline": cpu, "clocks": clocks}
     emit(line)
 
 

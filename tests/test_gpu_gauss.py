@@ -40,6 +40,33 @@ def test_fixture_known_answer_bit_exact(n, mode):
 
 
 @pytest.mark.parametrize("mode", MODES)
+def test_fixture_known_answer_at_scale(mode):
+    # the same known answer holds for ANY n (gauss_internal_input.c:45-48) and the fixture is exact in FP32 and TF32:
+    # a bit-exact check at a size where the CPU oracle would need minutes (3 outer blocks of 512, 64 inner blocks)
+    n = 8192
+    A, B = pkg.initMatrix(n)
+    X, Bafter = pkg.gauss(A, B, mode=mode, want_b_after=True)
+    wx, wb = fixture_answer(n)
+    assert np.array_equal(X, wx)
+    assert np.array_equal(Bafter, wb)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_opt_in_schedules_give_the_same_answer(mode, monkeypatch):
+    # GAUSS_CUDA_OVERLAP=1 (panel path on a priority stream beside the bulk update) and GAUSS_CUDA_GRAPH=0
+    # (plain launches instead of graph replay) are read when the context is created
+    n = 2100
+    A, B, Xtrue = pkg.initialize_inputs(n, 12)
+    X0 = pkg.gauss(A, B, mode=mode, nb=512)
+    monkeypatch.setenv("GAUSS_CUDA_OVERLAP", "1")
+    X1 = pkg.gauss(A, B, mode=mode, nb=512)
+    monkeypatch.setenv("GAUSS_CUDA_GRAPH", "0")
+    X2 = pkg.gauss(A, B, mode=mode, nb=512)
+    assert ol.max_rel_error(X0, Xtrue) <= TOL
+    assert np.array_equal(X0, X1) and np.array_equal(X1, X2)     # same kernels, same tile shapes, same order of sums
+
+
+@pytest.mark.parametrize("mode", MODES)
 @pytest.mark.parametrize("n,seed", [(64, 1), (200, 2), (512, 3), (1000, 1), (2048, 1)])
 def test_seeded_matches_oracle(n, seed, mode):
     A, B, Xtrue = pkg.initialize_inputs(n, seed)
