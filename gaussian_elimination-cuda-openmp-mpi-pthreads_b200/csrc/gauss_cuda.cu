@@ -133,6 +133,8 @@ struct gauss_cuda_ctx {
     float* la_hi[2] = {nullptr, nullptr};       // [rows_local x NB]  split L operand (3xTF32 mode);
     float* la_lo[2] = {nullptr, nullptr};       //                    second copy for the single-GPU look-ahead
     cudaStream_t s_panel = nullptr;             // higher-priority stream of the single-GPU look-ahead
+    cudaStream_t s_side = nullptr;              // side stream of the single-GPU schedule: P2(j) beside the rest of P1
+    cudaEvent_t ev_inner[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, ev_side = nullptr;
     cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
     bool overlap = false;
     int overlap_max_tiles = 6;
@@ -242,6 +244,11 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         }
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
+    if (world == 1 && !(getenv("GAUSS_CUDA_INNER_FORK") && atoi(getenv("GAUSS_CUDA_INNER_FORK")) == 0)) {
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_side, cudaStreamNonBlocking);
+        for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_inner[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming);
+    }
     if (c->overlap) {
         int lo_p = 0, hi_p = 0;
         cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p);
@@ -304,6 +311,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
     if (c->s_comm) cudaStreamSynchronize(c->s_comm);
     if (c->s_panel) cudaStreamSynchronize(c->s_panel);
+    if (c->s_side) cudaStreamSynchronize(c->s_side);
     float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi[0], c->la_lo[0], c->la_hi[1], c->la_lo[1],
                      c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
@@ -327,6 +335,9 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
         if (c->ev_join[i]) cudaEventDestroy(c->ev_join[i]);
     }
     if (c->s_panel) cudaStreamDestroy(c->s_panel);
+    for (auto& ev : c->ev_inner) if (ev) cudaEventDestroy(ev);
+    if (c->ev_side) cudaEventDestroy(c->ev_side);
+    if (c->s_side) cudaStreamDestroy(c->s_side);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     delete c;
 }
@@ -502,18 +513,62 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const S
     return GAUSS_CUDA_OK;
 }
 
-// Single GPU, one stream: P1 -> P2 -> P3 per outer block.
+// Single GPU: P1 -> P2 -> P3 per outer block.  P2 of inner block j (L-col solve of the rows below the panel and
+// their in-panel update) only needs the diagonal factor and U-row of block j, so it is forked onto a side stream
+// as soon as those are out and runs beside the rest of P1 (whose chain of small kernels -- diagonal factor, panel
+// L-col, panel update -- leaves most of the GPU idle); both streams join before P3.
 static int factor_single(gauss_cuda_ctx* c)
 {
-    const int ld = c->ld, NB = c->NB;
-    const StepBufs sb{c->s_main, c->la_hi[0], c->la_lo[0]};
+    cudaStream_t s = c->s_main, ss = c->s_side;
+    const int ld = c->ld, NB = c->NB, np = c->np;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    float* ubh = c->ub_hi[0]; float* ubl = c->ub_lo[0];
+    float* lah = c->la_hi[0]; float* lal = c->la_lo[0];
+    const StepBufs sb{s, lah, lal};
     for (int K = 0; K < c->nblk; ++K) {
-        int rc = panel_factor(c, K, c->ub_hi[0], c->ub_lo[0], sb);
-        if (rc) return rc;
-        const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + K * NB;
-        PanelRef pr{P0, ld, P0 + blk_rows(c, K), ld, c->ub_hi[0], c->ub_lo[0]};
-        const int l0 = first_local_block_after(c, K) * NB;
-        if ((rc = col_panel(c, K, pr, l0, sb))) return rc;
+        const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
+        float* P = c->W + (size_t)k0 * ld;
+        const int l0 = k0 + kb, m = np - l0;                       // rows below the panel
+        // (below ~4096 the two-branch CUDA graph costs more launch latency, ~0.2 ms, than the fork saves)
+        const bool fork = ss != nullptr && m > 0 && ninner <= 8 && np >= 4096;
+        float* Wb = c->W + (size_t)l0 * ld;
+        int rc;
+        for (int j = 0; j < ninner; ++j) {
+            const int kk = k0 + j * kNb, r = j * kNb;
+            launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
+            launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+                        tc ? ubh + (size_t)(kk + kNb) * NB : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB : nullptr, NB, r, s);
+            if (fork) {                                            // P2(j) beside the rest of P1
+                CK(cudaEventRecord(c->ev_inner[j], s));
+                CK(cudaStreamWaitEvent(ss, c->ev_inner[j], 0));
+                launch_lcol(P + (size_t)r * ld + kk, ld, Wb + kk, ld, m,
+                            tc ? lah + (size_t)l0 * NB : nullptr, tc ? lal + (size_t)l0 * NB : nullptr, NB, r, ss);
+                const int nin = kb - (r + kNb);
+                if (nin > 0) {
+                    rc = gemm_update(c, ss, Wb + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                                     tc ? lah + (size_t)l0 * NB + r : nullptr, tc ? lal + (size_t)l0 * NB + r : nullptr,
+                                     tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
+                                     Wb + kk + kNb, m, nin, kNb);
+                    if (rc) return rc;
+                }
+            }
+            const int mrem = kb - (r + kNb);
+            if (mrem > 0) {
+                launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
+                            tc ? lah + (size_t)(k0 + r + kNb) * NB : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB : nullptr, NB, r, s);
+                rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                                 tc ? lah + (size_t)(k0 + r + kNb) * NB + r : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB + r : nullptr,
+                                 tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
+                                 P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
+                if (rc) return rc;
+            }
+        }
+        const float* P0 = P + k0;
+        PanelRef pr{P0, ld, P0 + kb, ld, ubh, ubl};
+        if (fork) {
+            CK(cudaEventRecord(c->ev_side, ss));
+            CK(cudaStreamWaitEvent(s, c->ev_side, 0));
+        } else if ((rc = col_panel(c, K, pr, l0, sb))) return rc;
         if ((rc = trailing_update(c, K, pr, sb, l0, c->rows_local))) return rc;
     }
     return GAUSS_CUDA_OK;
