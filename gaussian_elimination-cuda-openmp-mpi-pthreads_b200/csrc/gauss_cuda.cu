@@ -249,7 +249,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_inner[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming);
     }
-    if (c->overlap) {
+    if (c->overlap || (world > 1 && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0))) {
         int lo_p = 0, hi_p = 0;
         cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p);
         if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->s_panel, cudaStreamNonBlocking, hi_p);
@@ -670,6 +670,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         if (mine) {                                               // the owner reads its panel in place
             const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + k0;
             pr = PanelRef{P0, ld, P0 + kb, ld, c->ub_hi[b], c->ub_lo[b]};
+            CK(cudaStreamWaitEvent(s, c->ev_ready[b], 0));        // ... once its factorisation (panel stream) is done
         } else {
             pr = PanelRef{c->pbuf[b], kb, c->pbuf[b] + (size_t)kb * kb, ld - k0 - kb, c->ub_hi[b], c->ub_lo[b]};
             CK(cudaStreamWaitEvent(s, c->ev_diag[b], 0));         // the diagonal region has arrived
@@ -682,18 +683,27 @@ static int factor_lookahead(gauss_cuda_ctx* c)
             if (tc) rebuild_split_u(c, K, pr, false);
         }
         int rest_lo = l0;
+        bool rest_bounded = false;
         if (K + 1 < c->nblk) {
             if (owner_of(K + 1) == c->rank) {
-                // block K+1 is this rank's first block below the panel: bring it up to date, factor it
+                // block K+1 is this rank's first block below the panel: bring it up to date, then factor it on the
+                // (higher-priority) panel stream while this stream carries on with the rest of the update
                 const int rows_next = blk_rows(c, K + 1);
                 if ((rc = trailing_update(c, K, pr, sbm, l0, l0 + rows_next))) return rc;
-                if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbm))) return rc;
-                CK(cudaEventRecord(c->ev_ready[b ^ 1], s));
+                cudaStream_t sp = c->s_panel ? c->s_panel : s;
+                if (sp != s) {
+                    CK(cudaEventRecord(c->ev_fork[b], s));
+                    CK(cudaStreamWaitEvent(sp, c->ev_fork[b], 0));
+                }
+                const StepBufs sbp{sp, c->la_hi[0], c->la_lo[0]};
+                if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbp))) return rc;
+                CK(cudaEventRecord(c->ev_ready[b ^ 1], sp));
                 rest_lo = l0 + rows_next;
+                rest_bounded = sp != s;
             }
             if ((rc = enqueue_bcast(K + 1))) return rc;
         }
-        if ((rc = trailing_update(c, K, pr, sbm, rest_lo, c->rows_local))) return rc;
+        if ((rc = trailing_update(c, K, pr, sbm, rest_lo, c->rows_local, -1, -1, rest_bounded ? c->overlap_max_tiles : 0))) return rc;
         CK(cudaEventRecord(c->ev_free[b], s));                    // pbuf[b] / ub[b] may be overwritten from here on
     }
     CK(cudaEventRecord(c->ev_done[0], sc));
