@@ -157,7 +157,7 @@ struct gauss_cuda_ctx {
     int* ipiv = nullptr;        // device: pivot row of every step
     cudaStream_t s_main = nullptr, s_comm = nullptr;
     cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
-    cudaEvent_t ev_diag[2] = {nullptr, nullptr};
+    cudaEvent_t ev_diag[2] = {nullptr, nullptr}, ev_cols[2] = {nullptr, nullptr}, ev_p2[2] = {nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     std::vector<cudaEvent_t> upd_ev;    // 2 per outer block: brackets of the trailing-update launches
     std::vector<double> upd_flops;
@@ -236,7 +236,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
         const size_t ub = (size_t)c->ld * c->NB * sizeof(float);
         A((void**)&c->la_hi[0], la); A((void**)&c->la_lo[0], la);
-        if (c->overlap) { A((void**)&c->la_hi[1], la); A((void**)&c->la_lo[1], la); }
+        if (c->overlap || world > 1) { A((void**)&c->la_hi[1], la); A((void**)&c->la_lo[1], la); }
         for (int i = 0; i < ((world > 1 || c->overlap) ? 2 : 1); ++i) {
             A((void**)&c->ub_hi[i], ub); A((void**)&c->ub_lo[i], ub);
             if (e == cudaSuccess) e = cudaMemset(c->ub_hi[i], 0, ub);
@@ -244,12 +244,13 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         }
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
-    if (world == 1 && !(getenv("GAUSS_CUDA_INNER_FORK") && atoi(getenv("GAUSS_CUDA_INNER_FORK")) == 0)) {
+    const bool dist_fork = world > 1 && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0);
+    if ((world == 1 && !(getenv("GAUSS_CUDA_INNER_FORK") && atoi(getenv("GAUSS_CUDA_INNER_FORK")) == 0)) || dist_fork) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_side, cudaStreamNonBlocking);
         for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_inner[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming);
     }
-    if (c->overlap || (world > 1 && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0))) {
+    if (c->overlap || dist_fork) {
         int lo_p = 0, hi_p = 0;
         cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p);
         if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->s_panel, cudaStreamNonBlocking, hi_p);
@@ -264,6 +265,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
             e = cudaEventCreateWithFlags(&c->ev_ready[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_diag[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_cols[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_p2[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_free[i], cudaEventDisableTiming);
         }
     }
@@ -327,6 +330,8 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
         if (c->ev_ready[i]) cudaEventDestroy(c->ev_ready[i]);
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
         if (c->ev_diag[i]) cudaEventDestroy(c->ev_diag[i]);
+        if (c->ev_cols[i]) cudaEventDestroy(c->ev_cols[i]);
+        if (c->ev_p2[i]) cudaEventDestroy(c->ev_p2[i]);
         if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
     }
     if (c->s_comm) cudaStreamDestroy(c->s_comm);
@@ -436,7 +441,7 @@ static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo, co
 
 // Non-owners in 3xTF32 mode: rebuild the split, transposed U operand from the raw broadcast panel;
 // `diag_part` selects the columns inside the panel (needed by P2) or right of it (needed by P3).
-static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr, bool diag_part)
+static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr, bool diag_part, cudaStream_t st)
 {
     const int NB = c->NB, k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
     for (int j = 0; j < ninner; ++j) {
@@ -446,11 +451,11 @@ static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr, bool d
             if (ncol > 0)
                 launch_split_transpose(pr.pd + (size_t)r * pr.ldd + cfirst, pr.ldd,
                                        pr.ub_hi + (size_t)(k0 + cfirst) * NB + r, pr.ub_lo + (size_t)(k0 + cfirst) * NB + r,
-                                       NB, kNb, ncol, kNb, c->s_main);
+                                       NB, kNb, ncol, kNb, st);
         } else {
             launch_split_transpose(pr.pu + (size_t)r * pr.ldu, pr.ldu,
                                    pr.ub_hi + (size_t)(k0 + kb) * NB + r, pr.ub_lo + (size_t)(k0 + kb) * NB + r,
-                                   NB, kNb, c->ld - k0 - kb, kNb, c->s_main);
+                                   NB, kNb, c->ld - k0 - kb, kNb, st);
         }
     }
 }
@@ -620,16 +625,32 @@ static int factor_overlap(gauss_cuda_ctx* c)
     return GAUSS_CUDA_OK;
 }
 
-// Multi-GPU with look-ahead.  The owner of block K+1 updates that block's rows first, factors the
-// panel and hands it to the communication stream, so the broadcast (the reference's per-step
-// MPI_Bcast, gauss_mpi :137) and the panel factorisation overlap with everybody's trailing update
-// of step K.  Panel buffers and split U operands are double buffered by the parity of K.
+// Multi-GPU with look-ahead.  While the bulk of the trailing update of step K runs on the main stream, the
+// whole panel path of step K+1 runs beside it:
+//   owner of K+1   row strip of P3(K) (the rows of block K+1) -> P1(K+1) on the panel stream -> packed panel
+//                  broadcast on the comm stream (diagonal region first, then U12: the reference's per-step
+//                  MPI_Bcast, gauss_mpi :137)
+//   every rank     column strip of P3(K) (the columns of block K+1) -> P2(K+1) on the side stream as soon as the
+//                  diagonal region has arrived
+// so that step K+1 finds its L21 ready and only waits for the U12 region.  Panel buffers and the split L21 / U12
+// operands are double buffered by the parity of K; the bulk update's CTAs give up their SM every few tiles so
+// the small kernels of the other streams get in.
 static int factor_lookahead(gauss_cuda_ctx* c)
 {
     cudaStream_t s = c->s_main, sc = c->s_comm;
+    cudaStream_t sp = c->s_panel ? c->s_panel : s;
+    cudaStream_t ss = c->s_side ? c->s_side : s;
     const int ld = c->ld, NB = c->NB;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     auto owner_of = [&](int K) { return K % c->world; };
+    auto panel_ref = [&](int K) -> PanelRef {
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
+        if (owner_of(K) == c->rank) {                             // the owner reads its panel in place
+            const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+            return PanelRef{P0, ld, P0 + kb, ld, c->ub_hi[b], c->ub_lo[b]};
+        }
+        return PanelRef{c->pbuf[b], kb, c->pbuf[b] + (size_t)kb * kb, ld - k0 - kb, c->ub_hi[b], c->ub_lo[b]};
+    };
     // enqueue on the comm stream: (owner) pack panel K, then broadcast it into pbuf[K&1] in two pieces --
     // the kb x kb diagonal region first (all that P2 needs), then the U12 region (needed by P3)
     auto enqueue_bcast = [&](int K) -> int {
@@ -638,7 +659,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         float* bufu = c->pbuf[b] + (size_t)kb * kb;
         CK(cudaStreamWaitEvent(sc, c->ev_free[b], 0));            // last readers of pbuf[b] are done
         if (owner_of(K) == c->rank) {
-            CK(cudaStreamWaitEvent(sc, c->ev_ready[b], 0));       // P1(K) finished on the main stream
+            CK(cudaStreamWaitEvent(sc, c->ev_ready[b], 0));       // P1(K) finished
             const float* P = c->W + (size_t)blk_local_row(c, K) * ld + k0;
             CK(cudaMemcpy2DAsync(bufd, (size_t)kb * sizeof(float), P, (size_t)ld * sizeof(float),
                                  (size_t)kb * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
@@ -652,59 +673,72 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         CK(cudaEventRecord(c->ev_done[b], sc));
         return GAUSS_CUDA_OK;
     };
+    // P2(K) on stream `st`: wait for the diagonal region (owner: its own factorisation), then the L-col chain
+    auto column_panel_on = [&](int K, cudaStream_t st) -> int {
+        const int b = K & 1;
+        const PanelRef pr = panel_ref(K);
+        if (owner_of(K) == c->rank) {
+            CK(cudaStreamWaitEvent(st, c->ev_ready[b], 0));
+        } else {
+            CK(cudaStreamWaitEvent(st, c->ev_diag[b], 0));
+            if (tc) rebuild_split_u(c, K, pr, true, st);
+        }
+        const StepBufs sbk{st, c->la_hi[b], c->la_lo[b]};
+        return col_panel(c, K, pr, first_local_block_after(c, K) * NB, sbk);
+    };
     int rc;
-    // both panel buffers start out free
-    CK(cudaEventRecord(c->ev_free[0], s));
+    CK(cudaEventRecord(c->ev_free[0], s));                        // both panel buffers start out free
     CK(cudaEventRecord(c->ev_free[1], s));
-    const StepBufs sbm{s, c->la_hi[0], c->la_lo[0]};
     if (owner_of(0) == c->rank) {
-        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sbm))) return rc;
+        const StepBufs sb0{s, c->la_hi[0], c->la_lo[0]};
+        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sb0))) return rc;
         CK(cudaEventRecord(c->ev_ready[0], s));
     }
     if ((rc = enqueue_bcast(0))) return rc;
+    if ((rc = column_panel_on(0, s))) return rc;                  // nothing to overlap with yet
     for (int K = 0; K < c->nblk; ++K) {
-        const int b = K & 1, k0 = K * NB;
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
         const bool mine = owner_of(K) == c->rank;
-        const int kb = blk_rows(c, K);
-        PanelRef pr;
-        if (mine) {                                               // the owner reads its panel in place
-            const float* P0 = c->W + (size_t)blk_local_row(c, K) * ld + k0;
-            pr = PanelRef{P0, ld, P0 + kb, ld, c->ub_hi[b], c->ub_lo[b]};
-            CK(cudaStreamWaitEvent(s, c->ev_ready[b], 0));        // ... once its factorisation (panel stream) is done
-        } else {
-            pr = PanelRef{c->pbuf[b], kb, c->pbuf[b] + (size_t)kb * kb, ld - k0 - kb, c->ub_hi[b], c->ub_lo[b]};
-            CK(cudaStreamWaitEvent(s, c->ev_diag[b], 0));         // the diagonal region has arrived
-            if (tc) rebuild_split_u(c, K, pr, true);
+        const PanelRef pr = panel_ref(K);
+        const StepBufs sbm{s, c->la_hi[b], c->la_lo[b]};
+        if (!mine) {
+            CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // the U12 region has arrived
+            if (tc) rebuild_split_u(c, K, pr, false, s);
         }
         const int l0 = first_local_block_after(c, K) * NB;
-        if ((rc = col_panel(c, K, pr, l0, sbm))) return rc;
-        if (!mine) {
-            CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // ... and now the U12 region
-            if (tc) rebuild_split_u(c, K, pr, false);
+        if (K + 1 >= c->nblk) {                                   // last block: nothing below it
+            CK(cudaEventRecord(c->ev_free[b], s));
+            break;
         }
-        int rest_lo = l0;
-        bool rest_bounded = false;
-        if (K + 1 < c->nblk) {
-            if (owner_of(K + 1) == c->rank) {
-                // block K+1 is this rank's first block below the panel: bring it up to date, then factor it on the
-                // (higher-priority) panel stream while this stream carries on with the rest of the update
-                const int rows_next = blk_rows(c, K + 1);
-                if ((rc = trailing_update(c, K, pr, sbm, l0, l0 + rows_next))) return rc;
-                cudaStream_t sp = c->s_panel ? c->s_panel : s;
-                if (sp != s) {
-                    CK(cudaEventRecord(c->ev_fork[b], s));
-                    CK(cudaStreamWaitEvent(sp, c->ev_fork[b], 0));
-                }
-                const StepBufs sbp{sp, c->la_hi[0], c->la_lo[0]};
-                if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbp))) return rc;
-                CK(cudaEventRecord(c->ev_ready[b ^ 1], sp));
-                rest_lo = l0 + rows_next;
-                rest_bounded = sp != s;
+        const int rows_next = blk_rows(c, K + 1), cnext = k0 + kb;
+        const bool own_next = owner_of(K + 1) == c->rank;
+        int l1 = l0;
+        if (own_next) {
+            // the rows of block K+1 first, then its factorisation on the panel stream
+            if ((rc = trailing_update(c, K, pr, sbm, l0, l0 + rows_next))) return rc;
+            if (sp != s) {
+                CK(cudaEventRecord(c->ev_fork[b], s));
+                CK(cudaStreamWaitEvent(sp, c->ev_fork[b], 0));
             }
-            if ((rc = enqueue_bcast(K + 1))) return rc;
+            const StepBufs sbp{sp, c->la_hi[b ^ 1], c->la_lo[b ^ 1]};
+            if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbp))) return rc;
+            CK(cudaEventRecord(c->ev_ready[b ^ 1], sp));
+            l1 = l0 + rows_next;
         }
-        if ((rc = trailing_update(c, K, pr, sbm, rest_lo, c->rows_local, -1, -1, rest_bounded ? c->overlap_max_tiles : 0))) return rc;
-        CK(cudaEventRecord(c->ev_free[b], s));                    // pbuf[b] / ub[b] may be overwritten from here on
+        if ((rc = enqueue_bcast(K + 1))) return rc;
+        // the columns of block K+1 for the rows below it, then P2(K+1) on the side stream
+        if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext, rows_next))) return rc;
+        if (ss != s) {
+            CK(cudaEventRecord(c->ev_cols[b], s));
+            CK(cudaStreamWaitEvent(ss, c->ev_cols[b], 0));
+        }
+        if ((rc = column_panel_on(K + 1, ss))) return rc;
+        if (ss != s) CK(cudaEventRecord(c->ev_p2[b ^ 1], ss));
+        // the bulk of the update beside all that
+        const bool beside = sp != s || ss != s;
+        if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1, beside ? c->overlap_max_tiles : 0))) return rc;
+        CK(cudaEventRecord(c->ev_free[b], s));                    // pbuf[b] / ub[b] / la[b] may be overwritten from here on
+        if (ss != s) CK(cudaStreamWaitEvent(s, c->ev_p2[b ^ 1], 0));
     }
     CK(cudaEventRecord(c->ev_done[0], sc));
     CK(cudaStreamWaitEvent(s, c->ev_done[0], 0));                 // join the comm stream
