@@ -137,7 +137,7 @@ struct gauss_cuda_ctx {
     cudaEvent_t ev_inner[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, ev_side = nullptr;
     cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
     bool overlap = false;
-    int overlap_max_tiles = 6;
+    int overlap_max_tiles = 3;
     float* ub_hi[2] = {nullptr, nullptr};       // [ld x NB]          split U operand, transposed;
     float* ub_lo[2] = {nullptr, nullptr};       //                    second copy only when world > 1 (look-ahead)
     float* xvec = nullptr;   // [np] solution
@@ -159,6 +159,8 @@ struct gauss_cuda_ctx {
     cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_diag[2] = {nullptr, nullptr}, ev_cols[2] = {nullptr, nullptr}, ev_p2[2] = {nullptr, nullptr};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool trace = false;                 // GAUSS_CUDA_TRACE=1: per-phase timestamps of the multi-GPU main stream
+    std::vector<cudaEvent_t> tr_ev;     // 6 per outer block
     std::vector<cudaEvent_t> upd_ev;    // 2 per outer block: brackets of the trailing-update launches
     std::vector<double> upd_flops;
     int upd_count = 0;
@@ -271,6 +273,11 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         }
     }
     for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    c->trace = world > 1 && getenv("GAUSS_CUDA_TRACE") && atoi(getenv("GAUSS_CUDA_TRACE")) != 0;
+    if (c->trace) {
+        c->tr_ev.assign(6 * (size_t)c->nblk, nullptr);
+        for (size_t i = 0; i < c->tr_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->tr_ev[i]);
+    }
     c->upd_ev.assign(6 * (size_t)c->nblk, nullptr);            // look-ahead splits the update in up to three launches
     c->upd_flops.assign(3 * (size_t)c->nblk, 0.0);
     for (size_t i = 0; i < c->upd_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->upd_ev[i]);
@@ -326,6 +333,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     if (c->ipiv) cudaFree(c->ipiv);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->upd_ev) if (e) cudaEventDestroy(e);
+    for (auto& e : c->tr_ev) if (e) cudaEventDestroy(e);
     for (int i = 0; i < 2; ++i) {
         if (c->ev_ready[i]) cudaEventDestroy(c->ev_ready[i]);
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
@@ -701,10 +709,14 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         const bool mine = owner_of(K) == c->rank;
         const PanelRef pr = panel_ref(K);
         const StepBufs sbm{s, c->la_hi[b], c->la_lo[b]};
+        auto mark = [&](int i) { if (c->trace) cudaEventRecord(c->tr_ev[6 * (size_t)K + i], s); };
+        mark(0);                                                  // step begins (previous bulk + P2 join done)
         if (!mine) {
             CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // the U12 region has arrived
+            mark(1);
             if (tc) rebuild_split_u(c, K, pr, false, s);
-        }
+        } else mark(1);
+        mark(2);
         const int l0 = first_local_block_after(c, K) * NB;
         if (K + 1 >= c->nblk) {                                   // last block: nothing below it
             CK(cudaEventRecord(c->ev_free[b], s));
@@ -725,6 +737,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
             CK(cudaEventRecord(c->ev_ready[b ^ 1], sp));
             l1 = l0 + rows_next;
         }
+        mark(3);                                                  // row strip issued (owner of K+1 only)
         if ((rc = enqueue_bcast(K + 1))) return rc;
         // the columns of block K+1 for the rows below it, then P2(K+1) on the side stream
         if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext, rows_next))) return rc;
@@ -732,12 +745,14 @@ static int factor_lookahead(gauss_cuda_ctx* c)
             CK(cudaEventRecord(c->ev_cols[b], s));
             CK(cudaStreamWaitEvent(ss, c->ev_cols[b], 0));
         }
+        mark(4);                                                  // column strip done
         if ((rc = column_panel_on(K + 1, ss))) return rc;
         if (ss != s) CK(cudaEventRecord(c->ev_p2[b ^ 1], ss));
         // the bulk of the update beside all that
         const bool beside = sp != s || ss != s;
         if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1, beside ? c->overlap_max_tiles : 0))) return rc;
         CK(cudaEventRecord(c->ev_free[b], s));                    // pbuf[b] / ub[b] / la[b] may be overwritten from here on
+        mark(5);                                                  // bulk done
         if (ss != s) CK(cudaStreamWaitEvent(s, c->ev_p2[b ^ 1], 0));
     }
     CK(cudaEventRecord(c->ev_done[0], sc));
@@ -838,6 +853,22 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
                 o.update_launches += 1;
             }
         }
+    }
+    if (c->trace && fac) {
+        // where the main stream's time went: [0->1] waiting for the U12 broadcast, [1->2] rebuilding the split,
+        // [2->3] row strip, [3->4] column strip, [4->5] bulk update, [5->next 0] waiting for P2 of the next panel
+        double acc[6] = {0, 0, 0, 0, 0, 0};
+        for (int K = 0; K + 1 < c->nblk; ++K) {
+            for (int i = 0; i < 6; ++i) {
+                cudaEvent_t a = c->tr_ev[6 * (size_t)K + i];
+                cudaEvent_t b2 = i < 5 ? c->tr_ev[6 * (size_t)K + i + 1] : c->tr_ev[6 * (size_t)(K + 1)];
+                float ms = 0.f;
+                if (cudaEventElapsedTime(&ms, a, b2) == cudaSuccess) acc[i] += ms;
+            }
+        }
+        cudaGetLastError();
+        fprintf(stderr, "[gauss_cuda trace] rank %d/%d: wait_U12 %.2f ms, rebuild %.2f, row_strip %.2f, col_strip %.2f, bulk %.2f, wait_P2 %.2f (factor %.2f ms)\n",
+                c->rank, c->world, acc[0], acc[1], acc[2], acc[3], acc[4], acc[5], o.factor_s * 1e3);
     }
     if (st) *st = o;
     return flag ? GAUSS_CUDA_ZERO_PIVOT : GAUSS_CUDA_OK;
