@@ -28,7 +28,7 @@ ABI_SYMBOLS = (
     "gauss_cuda_init", "gauss_cuda_unique_id", "gauss_cuda_init_dist", "gauss_cuda_solve",
     "gauss_cuda_upload", "gauss_cuda_solve_resident", "gauss_cuda_download",
     "gauss_cuda_compute_gauss", "gauss_cuda_solve_gauss", "gauss_cuda_download_factors",
-    "gauss_cuda_set_pivoting", "gauss_cuda_get_pivots", "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device", "matmul_cuda_device_noalloc",
+    "gauss_cuda_set_pivoting", "gauss_cuda_get_pivots", "gauss_cuda_solve_refined", "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device", "matmul_cuda_device_noalloc",
     "gauss_host_init_matrix", "gauss_host_initialize_inputs", "gauss_host_matmul_fill",
     "gauss_host_read_dat", "gauss_host_init_rhs", "gauss_host_free",
     "gauss_cuda_strerror", "gauss_cuda_last_error", "gauss_cuda_device_count",
@@ -44,6 +44,18 @@ class GaussStats(C.Structure):
         ("mode", C.c_int), ("rank", C.c_int), ("world", C.c_int),
         ("kernel_launches", C.c_longlong),
         ("update_s", C.c_double), ("update_flops", C.c_double), ("update_launches", C.c_int),
+    ]
+
+    def asdict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+class RefineInfo(C.Structure):
+    """gauss_cuda_refine_info (include/gauss_cuda.h)."""
+    _fields_ = [
+        ("iterations", C.c_int), ("converged", C.c_int), ("last_correction", C.c_double),
+        ("residual_inf", C.c_double), ("factor_s", C.c_double), ("refine_s", C.c_double),
+        ("kernel_launches", C.c_longlong),
     ]
 
     def asdict(self):
@@ -87,6 +99,7 @@ def lib():
         L.gauss_cuda_download_factors.argtypes = [vp, _fp]
         L.gauss_cuda_set_pivoting.argtypes = [vp, C.c_int]
         L.gauss_cuda_get_pivots.argtypes = [vp, C.POINTER(C.c_int)]
+        L.gauss_cuda_solve_refined.argtypes = [vp, _dp, _dp, _dp, C.c_int, C.c_double, C.POINTER(RefineInfo)]
         L.gauss_host_read_dat.argtypes = [C.c_char_p, C.POINTER(_dp)]
         L.gauss_host_init_rhs.argtypes = [_dp, _dp, _dp, C.c_int]
         L.gauss_host_init_rhs.restype = None
@@ -272,6 +285,20 @@ class GaussCuda:
         Bo = np.empty(self.n, np.float32) if want_b_after else None
         _check(lib().gauss_cuda_download(self._h, X.ctypes.data_as(_fp), Bo.ctypes.data_as(_fp) if want_b_after else None))
         return (X, Bo) if want_b_after else X
+
+    def gauss_refined(self, A, B, max_iters=20, tol=1e-14):
+        """gauss() in the reference's own precision: A, B double (double **matrix, *B,
+        gauss_internal_input.c:15-16), X double.  FP32 elimination on the GPU followed by iterative
+        refinement with double residuals (gauss_cuda_solve_refined).  Returns (X, RefineInfo)."""
+        A = np.ascontiguousarray(A, dtype=np.float64)
+        B = np.ascontiguousarray(B, dtype=np.float64)
+        if A.shape != (self.n, self.n) or B.shape != (self.n,):
+            raise ValueError("A must be n x n and B of length n")
+        X = np.empty(self.n, np.float64)
+        info = RefineInfo()
+        _check(lib().gauss_cuda_solve_refined(self._h, A.ctypes.data_as(_dp), B.ctypes.data_as(_dp),
+                                              X.ctypes.data_as(_dp), int(max_iters), float(tol), C.byref(info)))
+        return X, info
 
     def set_pivoting(self, enabled=True):
         """Partial pivoting as in the reference's external-input variant (gauss_external_input.c:123-148)."""

@@ -155,6 +155,10 @@ struct gauss_cuda_ctx {
     bool pivot = false;         // partial pivoting (external-input variant)
     float* pt = nullptr;        // packed panel scratch [128 x np]
     int* ipiv = nullptr;        // device: pivot row of every step
+    // iterative refinement (gauss_cuda_solve_refined), allocated on first use
+    double* A64 = nullptr;      // [n x n] the system in double
+    double* v64 = nullptr;      // b | x | r | 2 norms   (3n + 2 doubles)
+    float* rf32 = nullptr;      // r | y | d             (3 np floats)
     cudaStream_t s_main = nullptr, s_comm = nullptr;
     cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_diag[2] = {nullptr, nullptr}, ev_cols[2] = {nullptr, nullptr}, ev_p2[2] = {nullptr, nullptr};
@@ -331,6 +335,9 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     if (c->sched) cudaFree(c->sched);
     if (c->pt) cudaFree(c->pt);
     if (c->ipiv) cudaFree(c->ipiv);
+    if (c->A64) cudaFree(c->A64);
+    if (c->v64) cudaFree(c->v64);
+    if (c->rf32) cudaFree(c->rf32);
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->upd_ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->tr_ev) if (e) cudaEventDestroy(e);
@@ -1043,6 +1050,81 @@ extern "C" int gauss_cuda_download(gauss_cuda_ctx* c, float* X, float* B_out)
     int rc = download_results(c, X, B_out);
     if (rc) return rc;
     CK(cudaStreamSynchronize(c->s_main));
+    return GAUSS_CUDA_OK;
+}
+
+// Mixed-precision iterative refinement: the FP32 factors are the preconditioner, residuals and the solution
+// are kept in double.  Each sweep: r = b - A x (double), d = U^-1 L^-1 (float)r with the stored factors, x += d.
+extern "C" int gauss_cuda_solve_refined(gauss_cuda_ctx* c, const double* A, const double* B, double* X,
+                                        int max_iters, double tol, gauss_cuda_refine_info* info)
+{
+    if (!c || !A || !B || !X || max_iters < 0) return GAUSS_CUDA_BAD_ARG;
+    if (c->world != 1 || c->pivot) {
+        snprintf(g_err, sizeof g_err, "gauss_cuda_solve_refined: single-GPU contexts without pivoting only");
+        return GAUSS_CUDA_BAD_ARG;
+    }
+    CK(cudaSetDevice(c->device));
+    const int n = c->n, np = c->np, ld = c->ld;
+    if (!c->A64) {
+        CK(cudaMalloc((void**)&c->A64, (size_t)n * n * sizeof(double)));
+        CK(cudaMalloc((void**)&c->v64, ((size_t)3 * n + 2) * sizeof(double)));
+        CK(cudaMalloc((void**)&c->rf32, (size_t)3 * np * sizeof(float)));
+    }
+    double *b64 = c->v64, *x64 = c->v64 + n, *r64 = c->v64 + 2 * (size_t)n, *norms = c->v64 + 3 * (size_t)n;
+    float *rf = c->rf32, *yf = c->rf32 + np, *df = c->rf32 + 2 * (size_t)np;
+    g_launch_count = 0;
+    cudaStream_t s = c->s_main;
+    int rc;
+    CK(cudaEventRecord(c->ev[0], s));
+    CK(cudaMemcpyAsync(c->A64, A, (size_t)n * n * sizeof(double), cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(b64, B, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, s));
+    launch_f64_to_w(c->A64, b64, n, c->W, ld, np, s);
+    launch_pad_identity(c->W, ld, 0, 0, n, n, n, s);
+    if (np > n) launch_pad_identity(c->W, ld, n, n, np - n, n, 0, s);
+    CK(cudaMemsetAsync(x64, 0, (size_t)n * sizeof(double), s));
+    CK(cudaMemsetAsync(c->rf32, 0, (size_t)3 * np * sizeof(float), s));      // the padded tail of r stays zero
+    if ((rc = run_core(c))) return rc;                                      // FP32 factors in W, x0 in xvec
+    launch_refine_update(x64, c->xvec, n, norms, s);                        // x = (double)x0
+    CK(cudaEventRecord(c->ev[4], s));
+    rc = finish_stats(c, nullptr, true, true, true, false);
+    if (rc) return rc;                                                      // zero pivot: nothing to refine
+    double h[2] = {0.0, 0.0}, prev = 0.0;
+    int it = 0, converged = 0;
+    for (; it < max_iters; ++it) {
+        launch_residual_f64(c->A64, x64, b64, r64, rf, n, s);
+        launch_trsv_factor_solve(c->W, ld, np, rf, yf, true, c->trsv_ctrl, s);
+        launch_trsv_factor_solve(c->W, ld, np, yf, df, false, c->trsv_ctrl, s);
+        launch_refine_update(x64, df, n, norms, s);
+        CK(cudaMemcpyAsync(h, norms, sizeof h, cudaMemcpyDeviceToHost, s));
+        CK(cudaStreamSynchronize(s));
+        const double rel = h[1] > 0.0 ? h[0] / h[1] : h[0];
+        if (!(rel == rel) || (it > 0 && rel > prev)) {                       // NaN or growing corrections: not contracting
+            ++it; prev = rel; break;
+        }
+        prev = rel;
+        if (rel <= tol) { ++it; converged = 1; break; }
+    }
+    launch_residual_f64(c->A64, x64, b64, r64, rf, n, s);                   // the residual of the returned x, for info
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(X, x64, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, s));
+    CK(cudaEventRecord(c->ev[5], s));
+    CK(cudaStreamSynchronize(s));
+    c->factored = false;
+    if (info) {
+        std::vector<double> r((size_t)n);
+        CK(cudaMemcpy(r.data(), r64, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost));
+        double rmax = 0.0;
+        for (double v : r) rmax = std::max(rmax, std::fabs(v));
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->ev[4], c->ev[5]);
+        info->iterations = it;
+        info->converged = converged;
+        info->last_correction = prev;
+        info->residual_inf = rmax;
+        info->factor_s = c->last.h2d_s + c->last.factor_s + c->last.backsub_s;
+        info->refine_s = (double)ms * 1e-3;
+        info->kernel_launches = g_launch_count;
+    }
     return GAUSS_CUDA_OK;
 }
 

@@ -39,6 +39,13 @@ void launch_sgemm_nn(const float* A, int lda, const float* B, int ldb, float* C,
 // scratch (ticket + per-block flags), reset here.  W is not modified.
 void launch_trsv_fused(const float* W, int ld, int nrows, int ycol, float* x, int* ctrl, cudaStream_t s);
 void launch_trsv_gemv_wide(float* u, int ld, int ycol, const float* x, int nrows, int kw, cudaStream_t s);
+// Solves with the stored factors for a new right-hand side (device vectors of nrows floats): y = L^-1 rhs
+// (lower, L carries the pivots) or x = U^-1 rhs (unit upper).  W is not modified.
+void launch_trsv_factor_solve(const float* W, int ld, int nrows, const float* rhs, float* out, bool lower, int* ctrl, cudaStream_t s);
+// FP64 helpers of the iterative-refinement entry point (see gauss_cuda_solve_refined)
+void launch_f64_to_w(const double* A, const double* b, int n, float* w, int ld, int ycol, cudaStream_t s);
+void launch_residual_f64(const double* A, const double* x, const double* b, double* r, float* rf, int n, cudaStream_t s);
+void launch_refine_update(double* x, const float* d, int n, double* out, cudaStream_t s);
 
 // Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.
 void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s);

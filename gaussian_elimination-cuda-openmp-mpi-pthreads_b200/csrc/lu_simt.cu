@@ -162,8 +162,13 @@ __device__ __forceinline__ void st_release(int* p, int v) {
     asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+// LOWER = false: x = U^-1 y, U unit upper (solveGauss).  LOWER = true: y = L^-1 r, L lower with the pivots on its
+// diagonal (the forward half of a solve with the stored factors, used by the iterative-refinement entry point).
+// rhs != nullptr: the right-hand side is that vector instead of column `ycol` of W.
+template <bool LOWER>
 __global__ void __launch_bounds__(256, 1)
-trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, float* __restrict__ x, int* __restrict__ ctrl)
+trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, const float* __restrict__ rhs,
+                  float* __restrict__ x, int* __restrict__ ctrl)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     TrsvSmem& sm = *reinterpret_cast<TrsvSmem*>(smem_raw);
@@ -171,7 +176,8 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, floa
     const int nblk = nrows / kNb;
     if (tid == 0) sm.ticket = atomicAdd(&ctrl[0], 1);
     __syncthreads();
-    const int r = nblk - 1 - sm.ticket;      // my row block; every block J > r belongs to an earlier ticket
+    // my row block; every block it depends on belongs to an earlier ticket (so it is running or done)
+    const int r = LOWER ? sm.ticket : nblk - 1 - sm.ticket;
     int* flags = ctrl + 1;
     const float* Wr = W + (size_t)r * kNb * ld;
 
@@ -180,7 +186,7 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, floa
         const int rr = idx >> 5, c4 = (idx & 31) << 2;
         *reinterpret_cast<float4*>(&sm.U[rr][c4]) = __ldg(reinterpret_cast<const float4*>(Wr + (size_t)rr * ld + r * kNb + c4));
     }
-    if (tid < kNb) sm.v[tid] = Wr[(size_t)tid * ld + ycol];
+    if (tid < kNb) sm.v[tid] = rhs ? rhs[r * kNb + tid] : Wr[(size_t)tid * ld + ycol];
 
     // rows 16*warp .. 16*warp+15 of the block; per-lane partial dot products over the lane's 4 columns
     float part[16];
@@ -188,32 +194,43 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, floa
     for (int i = 0; i < 16; ++i) part[i] = 0.f;
     const float* rowbase = Wr + (size_t)(16 * warp) * ld + 4 * lane;
     float4 cur[16];
-    int J = nblk - 1;
-    if (J > r) {
+    const int Jfirst = LOWER ? 0 : nblk - 1, Jstep = LOWER ? 1 : -1;
+    const int nJ = LOWER ? r : nblk - 1 - r;                 // off-diagonal blocks of this block row
+    if (nJ > 0) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) cur[i] = __ldcs(reinterpret_cast<const float4*>(rowbase + (size_t)i * ld + J * kNb));
+        for (int i = 0; i < 16; ++i) cur[i] = __ldcs(reinterpret_cast<const float4*>(rowbase + (size_t)i * ld + Jfirst * kNb));
     }
     __syncthreads();
     if (warp < 4) {
-        // inverse of the 32x32 unit-upper diagonal sub-block `warp` (lane c: column c, bottom-up substitution)
+        // inverse of the 32x32 diagonal sub-block `warp`: lane c solves for column c of the inverse in registers
         const int o = 32 * warp;
         float xi[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) xi[i] = (i == lane) ? 1.f : 0.f;
+        if (LOWER) {
+            const float myrinv = 1.0f / sm.U[o + lane][o + lane];
 #pragma unroll
-        for (int j = 31; j > 0; --j) {
+            for (int j = 0; j < 32; ++j) {
+                xi[j] *= __shfl_sync(0xffffffffu, myrinv, j);
 #pragma unroll
-            for (int i = 0; i < j; ++i) xi[i] = fmaf(-sm.U[o + i][o + j], xi[j], xi[i]);
+                for (int i = j + 1; i < 32; ++i) xi[i] = fmaf(-sm.U[o + i][o + j], xi[j], xi[i]);
+            }
+        } else {
+#pragma unroll
+            for (int j = 31; j > 0; --j) {
+#pragma unroll
+                for (int i = 0; i < j; ++i) xi[i] = fmaf(-sm.U[o + i][o + j], xi[j], xi[i]);
+            }
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) sm.invT[warp][lane][i] = xi[i];
     }
 
-    for (; J > r; --J) {
+    for (int jj = 0, J = Jfirst; jj < nJ; ++jj, J += Jstep) {
         float4 nxt[16];
-        if (J - 1 > r) {                      // prefetch the next block of U before waiting for x_J
+        if (jj + 1 < nJ) {                    // prefetch the next block before waiting for x_J
 #pragma unroll
-            for (int i = 0; i < 16; ++i) nxt[i] = __ldcs(reinterpret_cast<const float4*>(rowbase + (size_t)i * ld + (J - 1) * kNb));
+            for (int i = 0; i < 16; ++i) nxt[i] = __ldcs(reinterpret_cast<const float4*>(rowbase + (size_t)i * ld + (J + Jstep) * kNb));
         }
         if (lane == 0) {                      // bounded wait: a protocol bug must trap, never hang the GPU
             const long long t0 = clock64();
@@ -229,7 +246,7 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, floa
             part[i] = fmaf(cur[i].x, xv.x, part[i]); part[i] = fmaf(cur[i].y, xv.y, part[i]);
             part[i] = fmaf(cur[i].z, xv.z, part[i]); part[i] = fmaf(cur[i].w, xv.w, part[i]);
         }
-        if (J - 1 > r) {
+        if (jj + 1 < nJ) {
 #pragma unroll
             for (int i = 0; i < 16; ++i) cur[i] = nxt[i];
         }
@@ -245,8 +262,10 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, floa
     __syncthreads();
     if (tid < kNb) sm.v[tid] -= sm.red[tid];
     __syncthreads();
-    // diagonal block: x_b = inv(U_bb) * v_b, then v_c -= U_cb * x_b for the sub-blocks above, b = 3..0
-    for (int b = 3; b >= 0; --b) {
+    // diagonal block: x_b = inv(D_bb) * v_b, then the other sub-blocks' v -= (off-diagonal sub-block) * x_b;
+    // b runs 3..0 for the upper solve and 0..3 for the lower one
+    for (int bi = 0; bi < 4; ++bi) {
+        const int b = LOWER ? bi : 3 - bi;
         if (warp == b) {
             float acc = 0.f;
 #pragma unroll 8
@@ -255,7 +274,7 @@ trsv_fused_kernel(const float* __restrict__ W, int ld, int nrows, int ycol, floa
             sm.v[32 * b + lane] = acc;
         }
         __syncthreads();
-        if (warp < b) {
+        if (warp < 4 && (LOWER ? warp > b : warp < b)) {
             float acc = sm.v[tid];
 #pragma unroll 8
             for (int k = 0; k < 32; ++k) acc = fmaf(-sm.U[tid][32 * b + k], sm.v[32 * b + k], acc);
@@ -273,7 +292,86 @@ void launch_trsv_fused(const float* W, int ld, int nrows, int ycol, float* x, in
 {
     const int nblk = nrows / kNb;
     cudaMemsetAsync(ctrl, 0, (size_t)(nblk + 1) * sizeof(int), s);
-    trsv_fused_kernel<<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, nrows, ycol, x, ctrl);
+    trsv_fused_kernel<false><<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, nrows, ycol, nullptr, x, ctrl);
+    ++g_launch_count;
+}
+
+// Solve with the stored factors for a new right-hand side (single GPU):  y = L^-1 rhs  (lower = true) or
+// x = U^-1 rhs (lower = false); rhs and out are device vectors of nrows floats, W is not modified.
+void launch_trsv_factor_solve(const float* W, int ld, int nrows, const float* rhs, float* out, bool lower, int* ctrl, cudaStream_t s)
+{
+    const int nblk = nrows / kNb;
+    cudaMemsetAsync(ctrl, 0, (size_t)(nblk + 1) * sizeof(int), s);
+    if (lower) trsv_fused_kernel<true><<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, nrows, 0, rhs, out, ctrl);
+    else       trsv_fused_kernel<false><<<nblk, 256, sizeof(TrsvSmem), s>>>(W, ld, nrows, 0, rhs, out, ctrl);
+    ++g_launch_count;
+}
+
+// ---- FP64 helpers of the iterative-refinement entry point --------------------------------------
+// W[i][j] = (float)A[i][j] for i, j < n (A row-major n x n doubles), RHS column `ycol` = (float)b[i]
+__global__ void f64_to_w_kernel(const double* __restrict__ A, const double* __restrict__ b, int n, float* __restrict__ w, int ld, int ycol)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j < n) w[(size_t)i * ld + j] = (float)A[(size_t)i * n + j];
+    if (j == 0) w[(size_t)i * ld + ycol] = (float)b[i];
+}
+// r = b - A x in double (a warp per row), rf[i] = (float)r[i]; rows n..np-1 of rf are zeroed by the caller
+__global__ void __launch_bounds__(256)
+residual_f64_kernel(const double* __restrict__ A, const double* __restrict__ x, const double* __restrict__ b,
+                    double* __restrict__ r, float* __restrict__ rf, int n)
+{
+    const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= n) return;
+    const double* a = A + (size_t)row * n;
+    double acc = 0.0;
+    for (int j = lane; j < n; j += 32) acc = fma(a[j], x[j], acc);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+    if (lane == 0) { const double rr = b[row] - acc; r[row] = rr; rf[row] = (float)rr; }
+}
+// x += d (d float), and the two norms the stopping test needs: out[0] = max|d|, out[1] = max|x| (one block)
+__global__ void __launch_bounds__(1024)
+refine_update_kernel(double* __restrict__ x, const float* __restrict__ d, int n, double* __restrict__ out)
+{
+    __shared__ double sd[32], sx[32];
+    double md = 0.0, mx = 0.0;
+    for (int i = threadIdx.x; i < n; i += 1024) {
+        const double di = (double)d[i];
+        const double xi = x[i] + di;
+        x[i] = xi;
+        md = fmax(md, fabs(di)); mx = fmax(mx, fabs(xi));
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        md = fmax(md, __shfl_xor_sync(0xffffffffu, md, off));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+    }
+    if ((threadIdx.x & 31) == 0) { sd[threadIdx.x >> 5] = md; sx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        md = sd[threadIdx.x]; mx = sx[threadIdx.x];
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            md = fmax(md, __shfl_xor_sync(0xffffffffu, md, off));
+            mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, off));
+        }
+        if (threadIdx.x == 0) { out[0] = md; out[1] = mx; }
+    }
+}
+void launch_f64_to_w(const double* A, const double* b, int n, float* w, int ld, int ycol, cudaStream_t s)
+{
+    dim3 grid((n + 255) / 256, n);
+    f64_to_w_kernel<<<grid, 256, 0, s>>>(A, b, n, w, ld, ycol);
+    ++g_launch_count;
+}
+void launch_residual_f64(const double* A, const double* x, const double* b, double* r, float* rf, int n, cudaStream_t s)
+{
+    residual_f64_kernel<<<(n + 7) / 8, 256, 0, s>>>(A, x, b, r, rf, n);
+    ++g_launch_count;
+}
+void launch_refine_update(double* x, const float* d, int n, double* out, cudaStream_t s)
+{
+    refine_update_kernel<<<1, 1024, 0, s>>>(x, d, n, out);
     ++g_launch_count;
 }
 
@@ -415,7 +513,8 @@ void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int
 void simt_setup_device()
 {
     panel_setup_device();
-    cudaFuncSetAttribute(trsv_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TrsvSmem));
+    cudaFuncSetAttribute(trsv_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TrsvSmem));
+    cudaFuncSetAttribute(trsv_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TrsvSmem));
 }
 
 } // namespace gb200

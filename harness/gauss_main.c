@@ -26,6 +26,8 @@ static float *A32, *B32, *X32, *Bafter32;
 static gauss_cuda_ctx *ctx;
 static gauss_cuda_stats stats;
 static int g_mode = GAUSS_CUDA_MODE_3XTF32;
+static int g_refine = 0;          /* -r: double-precision answers through gauss_cuda_solve_refined */
+static gauss_cuda_refine_info rinfo;
 
 static void die_on(int status, const char *where)
 {
@@ -82,25 +84,39 @@ void solveGauss(int nsize)
     for (int i = 0; i < nsize; ++i) { V[i] = C[i] = X32[i]; B[i] = Bafter32[i]; }
 }
 
-void gauss(int nsize) { computeGauss(nsize); solveGauss(nsize); }
+/* -r: the reference's double data goes to the library as it is; C comes back in double. */
+static void gauss_refined(int nsize)
+{
+    die_on(gauss_cuda_solve_refined(ctx, matrix[0], B, C, 20, 1e-14, &rinfo), "gauss_cuda_solve_refined");
+    die_on(gauss_cuda_download(ctx, NULL, Bafter32), "gauss_cuda_download");
+    for (int i = 0; i < nsize; ++i) { V[i] = C[i]; B[i] = Bafter32[i]; }
+}
+
+void gauss(int nsize)
+{
+    if (g_refine) { gauss_refined(nsize); return; }
+    computeGauss(nsize); solveGauss(nsize);
+}
 
 static void usage(const char *p)
 {
-    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v]   (reference form)\n"
+    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v] [-r]   (reference form)\n"
            "       %s N [seed]                                               (seeded form)\n"
-           "  -m 0 = tcgen05 3xTF32 (default), 1 = FFMA;  -v prints B[i] C[i] like VERIFY\n", p, p);
+           "  -m 0 = tcgen05 3xTF32 (default), 1 = FFMA;  -v prints B[i] C[i] like VERIFY;\n"
+           "  -r = double-precision answers (FP32 elimination + iterative refinement)\n", p, p);
 }
 
 int main(int argc, char *argv[])
 {
     int nsize = 2048, verify = 0, seeded = 0, opt;
     unsigned seed = 1;
-    while ((opt = getopt(argc, argv, "hs:t:m:v")) != -1) {
+    while ((opt = getopt(argc, argv, "hs:t:m:vr")) != -1) {
         switch (opt) {
             case 's': { int s = atoi(optarg); if (s > 0) nsize = s; else fprintf(stderr, "Entered size is negative, hence using the default (%d)\n", 2048); } break;
             case 't': if (atoi(optarg) <= 0) { fprintf(stderr, "Error: Threads count should be a natural number. \n"); return 0; } break;
             case 'm': g_mode = atoi(optarg) ? GAUSS_CUDA_MODE_FFMA : GAUSS_CUDA_MODE_3XTF32; break;
             case 'v': verify = 1; break;
+            case 'r': g_refine = 1; break;
             case 'h': usage(argv[0]); return 0;
             default:  usage(argv[0]); return 1;
         }
@@ -126,9 +142,14 @@ int main(int argc, char *argv[])
 
     /* extra lines (not in the reference) */
     const double flop = 2.0 / 3.0 * (double)nsize * nsize * nsize;
-    printf("GPU elimination: %.6f s (%.1f GFLOP/s, 2/3 N^3), back substitution: %.6f s, mode %s, outer block %d\n",
-           stats.factor_s, flop / stats.factor_s * 1e-9, stats.backsub_s,
-           g_mode == GAUSS_CUDA_MODE_FFMA ? "FFMA" : "3xTF32", stats.nb_outer);
+    if (g_refine)
+        printf("GPU FP32 solve incl. upload: %.6f s, refinement: %d sweeps in %.6f s (%s, last correction %.2e, residual %.2e)\n",
+               rinfo.factor_s, rinfo.iterations, rinfo.refine_s, rinfo.converged ? "converged" : "NOT converged",
+               rinfo.last_correction, rinfo.residual_inf);
+    else
+        printf("GPU elimination: %.6f s (%.1f GFLOP/s, 2/3 N^3), back substitution: %.6f s, mode %s, outer block %d\n",
+               stats.factor_s, flop / stats.factor_s * 1e-9, stats.backsub_s,
+               g_mode == GAUSS_CUDA_MODE_FFMA ? "FFMA" : "3xTF32", stats.nb_outer);
     double err = 0.0;
     if (seeded) {                              /* the reference's error metric, gauss_external_input.c:246-253 */
         for (int i = 0; i < nsize; ++i) { double e = fabs((C[i] - X_true[i]) / X_true[i]); if (e > err) err = e; }
@@ -142,5 +163,5 @@ int main(int argc, char *argv[])
         printf("Known-answer max abs error: %e\n", err);
     }
     gauss_cuda_free(ctx);
-    return err <= 1e-3 ? 0 : 3;
+    return err <= (g_refine ? 1e-8 : 1e-3) ? 0 : 3;
 }

@@ -117,6 +117,27 @@ int gauss_cuda_download_factors(gauss_cuda_ctx *ctx, float *LU);
 int gauss_cuda_set_pivoting(gauss_cuda_ctx *ctx, int enabled);
 int gauss_cuda_get_pivots(gauss_cuda_ctx *ctx, int *pivot_rows /* host, n */);
 
+/* Double-precision results from the FP32 factors.  The reference computes in double
+ * (double **matrix, *B, *C, gauss_internal_input.c:15-16); this entry takes and returns doubles and reaches the
+ * reference's accuracy by mixed-precision iterative refinement: A is rounded to FP32 and eliminated exactly as in
+ * gauss_cuda_solve (computeGauss :118-141), then x is corrected in sweeps  r = b - A x  (double, on the device),
+ * d = U^-1 L^-1 r  (the stored FP32 factors, two triangular solves -- solveGauss :144-159 and its forward
+ * counterpart), x += d, until  max|d| <= tol * max|x|,  the corrections stop shrinking, or max_iters sweeps ran.
+ * Converges when cond(A) * 2^-24 is well below 1 (the reference's own inputs are); `converged` says whether the
+ * tolerance was met.  A, B, X: host, n*n / n / n doubles.  Single-GPU contexts without pivoting only.
+ * Device memory for the double copy of A (8 n^2 bytes) is allocated on the first call and kept by the context. */
+typedef struct gauss_cuda_refine_info {
+    int iterations;            /* refinement sweeps done */
+    int converged;             /* 1: last max|d|/max|x| <= tol */
+    double last_correction;    /* max|d| / max|x| of the last sweep */
+    double residual_inf;       /* max_i |b - A x|_i of the returned x, in double */
+    double factor_s;           /* upload + FP32 elimination + first back substitution, seconds */
+    double refine_s;           /* all sweeps + download, seconds */
+    long long kernel_launches;
+} gauss_cuda_refine_info;
+int gauss_cuda_solve_refined(gauss_cuda_ctx *ctx, const double *A, const double *B, double *X,
+                             int max_iters, double tol, gauss_cuda_refine_info *info /* may be NULL */);
+
 void gauss_cuda_free(gauss_cuda_ctx *ctx);
 
 /* ---- FP32 matrix multiply -------------------------------------------------------------- */

@@ -1,0 +1,103 @@
+"""GPU parity of the double-precision entry point (gauss_cuda_solve_refined) against the oracle.
+
+The reference computes in double (gauss_internal_input.c:15-16).  The FP32 entry points are held to the
+north_star's 1e-3; this one - FP32 elimination plus iterative refinement with double residuals - is held to
+the reference's own precision: 1e-10 relative against the oracle's (and the reference's golden) double X,
+element-wise, where the FP32 paths need a norm-wise or bounded-range comparison.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_lib as ol
+from _pkg import pkg
+
+pytestmark = pytest.mark.gpu
+MODES = [pkg.MODE_FFMA, pkg.MODE_3XTF32]
+TOL64 = 1e-10
+
+
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_vectors.npz"))
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n,seed", [(64, 1), (200, 2), (777, 5), (2048, 1)])
+def test_seeded_matches_oracle_in_double(n, seed, mode):
+    A, B, Xtrue = pkg.initialize_inputs(n, seed)
+    Xref, _, _ = ol.gauss(A, B, nthreads=8)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        X, info = g.gauss_refined(A, B)
+        X32 = g.gauss(A, B)                                # the FP32 entry point still works on the same context
+    assert info.converged == 1 and 1 <= info.iterations <= 10
+    assert ol.max_rel_error(X, Xref) <= TOL64
+    assert ol.max_rel_error(X, Xtrue) <= 1e-8              # x = 1..n, element-wise (out of reach in FP32 at n >= 8192)
+    assert np.max(np.abs(B - A @ X)) == pytest.approx(info.residual_inf, rel=1e-3, abs=1e-18)
+    # the refined answer is an improvement on the plain one by orders of magnitude
+    assert ol.max_rel_error(X, Xref) * 1e3 < max(ol.max_rel_error(X32.astype(np.float64), Xref), 1e-12)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_golden_vectors_in_double(golden, mode):
+    for seed, n in ((1, 48), (2, 64), (3, 96)):
+        A, B = golden[f"seed{seed}_n{n}_A"], golden[f"seed{seed}_n{n}_B"]
+        with pkg.GaussCuda(n, mode=mode) as g:
+            X, info = g.gauss_refined(A, B)
+        assert info.converged == 1
+        assert ol.max_rel_error(X, golden[f"seed{seed}_n{n}_X"]) <= TOL64
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n", [8, 300, 1000])
+def test_fixture_known_answer(n, mode):
+    # gauss_internal_input.c:45-48: C = -0.5, 0, ..., 0, 0.5 - already exact in FP32, so one sweep confirms it
+    A, B = pkg.initMatrix(n)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        X, info = g.gauss_refined(A, B)
+    want = np.zeros(n)
+    want[0], want[-1] = -0.5, 0.5
+    assert np.array_equal(X, want)
+    assert info.converged == 1 and info.iterations == 1 and info.residual_inf == 0.0
+
+
+def test_zero_sweeps_is_the_fp32_answer():
+    n = 500
+    A, B, _ = pkg.initialize_inputs(n, 3)
+    with pkg.GaussCuda(n) as g:
+        X0, info = g.gauss_refined(A, B, max_iters=0)
+        X32 = g.gauss(A, B)
+    assert info.iterations == 0 and info.converged == 0
+    assert np.array_equal(X0, X32.astype(np.float64))
+
+
+def test_double_only_information_is_recovered():
+    # a right-hand side FP32 cannot even represent: b = A x with x = 1 + k * 2^-40.  The FP32 entry point sees x = 1.
+    n = 640
+    A, _, _ = pkg.initialize_inputs(n, 7)
+    x = 1.0 + np.arange(n) * 2.0 ** -40
+    B = A @ x
+    with pkg.GaussCuda(n) as g:
+        X, info = g.gauss_refined(A, B)
+    assert info.converged == 1
+    assert np.max(np.abs(X - x)) <= 1e-11
+    assert np.max(np.abs(X - 1.0)) > 1e-10
+
+
+def test_rejected_configurations():
+    n = 64
+    A, B, _ = pkg.initialize_inputs(n, 1)
+    with pkg.GaussCuda(n) as g:
+        g.set_pivoting(True)
+        with pytest.raises(pkg.GaussCudaError):
+            g.gauss_refined(A, B)
+        g.set_pivoting(False)
+        with pytest.raises(pkg.GaussCudaError):
+            g.gauss_refined(A, B, max_iters=-1)
+        A0 = A.copy()
+        A0[0, 0] = 0.0                                     # the reference's "The matrix is singular" (:86-89)
+        with pytest.raises(pkg.SingularMatrix):
+            g.gauss_refined(A0, B)
+        X, info = g.gauss_refined(A, B)                    # and the context is still usable
+    assert info.converged == 1
