@@ -155,6 +155,16 @@ struct gauss_cuda_ctx {
     bool pivot = false;         // partial pivoting (external-input variant)
     float* pt = nullptr;        // packed panel scratch [128 x np]
     int* ipiv = nullptr;        // device: pivot row of every step
+    // upload overlapped with the elimination (gauss_cuda_solve on a single GPU, see factor_streamed)
+    bool stream_on = true;      // GAUSS_CUDA_STREAM=0 switches it off
+    int stream_min_n = 16384;   // GAUSS_CUDA_STREAM_MIN_N: smaller systems upload first and replay the graph
+    int stream_chunks = 0;      // GAUSS_CUDA_STREAM_CHUNKS: > 0 = that many equal row chunks; 0 = graded (small first)
+    cudaStream_t s_copy = nullptr;
+    std::vector<cudaEvent_t> ev_chunk;
+    cudaEvent_t ev_gate = nullptr, ev_h2d_done = nullptr;
+    float* ub_all_hi = nullptr; // [nblk][ld x NB] split U operand of every panel (3xTF32 mode)
+    float* ub_all_lo = nullptr;
+    bool last_streamed = false;
     // iterative refinement (gauss_cuda_solve_refined), allocated on first use
     double* A64 = nullptr;      // [n x n] the system in double
     double* v64 = nullptr;      // b | x | r | 2 norms   (3n + 2 doubles)
@@ -213,6 +223,9 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         const char* mt = getenv("GAUSS_CUDA_OVERLAP_TILES");
         if (mt && atoi(mt) > 0) c->overlap_max_tiles = atoi(mt);
     }
+    { const char* e = getenv("GAUSS_CUDA_STREAM"); if (e && atoi(e) == 0) c->stream_on = false; }
+    { const char* e = getenv("GAUSS_CUDA_STREAM_MIN_N"); if (e) c->stream_min_n = atoi(e); }
+    { const char* e = getenv("GAUSS_CUDA_STREAM_CHUNKS"); if (e && atoi(e) > 0) c->stream_chunks = atoi(e); }
     c->np = round_up(n, kNb);
     c->ld = c->np + kPadCols;
     if (nb == 0) {
@@ -335,6 +348,12 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     if (c->sched) cudaFree(c->sched);
     if (c->pt) cudaFree(c->pt);
     if (c->ipiv) cudaFree(c->ipiv);
+    if (c->s_copy) { cudaStreamSynchronize(c->s_copy); cudaStreamDestroy(c->s_copy); }
+    for (auto& e : c->ev_chunk) if (e) cudaEventDestroy(e);
+    if (c->ev_gate) cudaEventDestroy(c->ev_gate);
+    if (c->ev_h2d_done) cudaEventDestroy(c->ev_h2d_done);
+    if (c->ub_all_hi) cudaFree(c->ub_all_hi);
+    if (c->ub_all_lo) cudaFree(c->ub_all_lo);
     if (c->A64) cudaFree(c->A64);
     if (c->v64) cudaFree(c->v64);
     if (c->rf32) cudaFree(c->rf32);
@@ -366,12 +385,12 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
 // host <-> device
 // ------------------------------------------------------------------------------------------
 // Copies this rank's rows of [A | b] into `dst` (same shape as W) and writes the identity padding.
-static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const float* B)
+// Outer blocks [R0, R1) of this rank; the RHS entries come from hvec (already on the device, same stream order).
+static int upload_blocks(gauss_cuda_ctx* c, float* dst, const float* A, int R0, int R1, cudaStream_t s)
 {
-    cudaStream_t s = c->s_main;
     const int n = c->n;
-    CK(cudaMemcpyAsync(c->hvec, B, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, s));
-    for (int R = c->rank; R < c->nblk; R += c->world) {
+    for (int R = R0; R < R1; ++R) {
+        if (R % c->world != c->rank) continue;
         const int g0 = R * c->NB, l0 = blk_local_row(c, R), rows = blk_rows(c, R);
         const int real = std::max(0, std::min(rows, n - g0));
         if (real > 0) {
@@ -386,6 +405,12 @@ static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const floa
     }
     CK(cudaGetLastError());
     return GAUSS_CUDA_OK;
+}
+
+static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const float* B)
+{
+    CK(cudaMemcpyAsync(c->hvec, B, (size_t)c->n * sizeof(float), cudaMemcpyHostToDevice, c->s_main));
+    return upload_blocks(c, dst, A, 0, c->nblk, c->s_main);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -475,14 +500,14 @@ static void rebuild_split_u(gauss_cuda_ctx* c, int K, const PanelRef& pr, bool d
     }
 }
 
-// P2: L-col solves and in-panel updates for the local rows [row_lo, rows_local).
-static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo, const StepBufs& sb)
+// P2: L-col solves and in-panel updates for the local rows [row_lo, row_hi)  (row_hi < 0: to the last local row).
+static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo, const StepBufs& sb, int row_hi = -1)
 {
     cudaStream_t s = sb.s;
     const int ld = c->ld, NB = c->NB;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
-    const int m = c->rows_local - row_lo;
+    const int m = (row_hi < 0 ? c->rows_local : row_hi) - row_lo;
     if (m <= 0) return GAUSS_CUDA_OK;
     float* Wb = c->W + (size_t)row_lo * ld;
     for (int j = 0; j < ninner; ++j) {
@@ -537,60 +562,135 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const S
 // their in-panel update) only needs the diagonal factor and U-row of block j, so it is forked onto a side stream
 // as soon as those are out and runs beside the rest of P1 (whose chain of small kernels -- diagonal factor, panel
 // L-col, panel update -- leaves most of the GPU idle); both streams join before P3.
-static int factor_single(gauss_cuda_ctx* c)
+static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* ubl)
 {
     cudaStream_t s = c->s_main, ss = c->s_side;
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
-    float* ubh = c->ub_hi[0]; float* ubl = c->ub_lo[0];
     float* lah = c->la_hi[0]; float* lal = c->la_lo[0];
     const StepBufs sb{s, lah, lal};
-    for (int K = 0; K < c->nblk; ++K) {
-        const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
-        float* P = c->W + (size_t)k0 * ld;
-        const int l0 = k0 + kb, m = np - l0;                       // rows below the panel
-        // (below ~4096 the two-branch CUDA graph costs more launch latency, ~0.2 ms, than the fork saves)
-        const bool fork = ss != nullptr && m > 0 && ninner <= 8 && np >= 4096;
-        float* Wb = c->W + (size_t)l0 * ld;
-        int rc;
-        for (int j = 0; j < ninner; ++j) {
-            const int kk = k0 + j * kNb, r = j * kNb;
-            launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
-            launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
-                        tc ? ubh + (size_t)(kk + kNb) * NB : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB : nullptr, NB, r, s);
-            if (fork) {                                            // P2(j) beside the rest of P1
-                CK(cudaEventRecord(c->ev_inner[j], s));
-                CK(cudaStreamWaitEvent(ss, c->ev_inner[j], 0));
-                launch_lcol(P + (size_t)r * ld + kk, ld, Wb + kk, ld, m,
-                            tc ? lah + (size_t)l0 * NB : nullptr, tc ? lal + (size_t)l0 * NB : nullptr, NB, r, ss);
-                const int nin = kb - (r + kNb);
-                if (nin > 0) {
-                    rc = gemm_update(c, ss, Wb + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
-                                     tc ? lah + (size_t)l0 * NB + r : nullptr, tc ? lal + (size_t)l0 * NB + r : nullptr,
-                                     tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
-                                     Wb + kk + kNb, m, nin, kNb);
-                    if (rc) return rc;
-                }
-            }
-            const int mrem = kb - (r + kNb);
-            if (mrem > 0) {
-                launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
-                            tc ? lah + (size_t)(k0 + r + kNb) * NB : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB : nullptr, NB, r, s);
-                rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
-                                 tc ? lah + (size_t)(k0 + r + kNb) * NB + r : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB + r : nullptr,
+    const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
+    float* P = c->W + (size_t)k0 * ld;
+    const int l0 = k0 + kb, m = row_hi - l0;                   // rows below the panel (of those present)
+    // (below ~4096 the two-branch CUDA graph costs more launch latency, ~0.2 ms, than the fork saves)
+    const bool fork = ss != nullptr && m > 0 && ninner <= 8 && np >= 4096;
+    float* Wb = c->W + (size_t)l0 * ld;
+    int rc;
+    for (int j = 0; j < ninner; ++j) {
+        const int kk = k0 + j * kNb, r = j * kNb;
+        launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
+        launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+                    tc ? ubh + (size_t)(kk + kNb) * NB : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB : nullptr, NB, r, s);
+        if (fork) {                                            // P2(j) beside the rest of P1
+            CK(cudaEventRecord(c->ev_inner[j], s));
+            CK(cudaStreamWaitEvent(ss, c->ev_inner[j], 0));
+            launch_lcol(P + (size_t)r * ld + kk, ld, Wb + kk, ld, m,
+                        tc ? lah + (size_t)l0 * NB : nullptr, tc ? lal + (size_t)l0 * NB : nullptr, NB, r, ss);
+            const int nin = kb - (r + kNb);
+            if (nin > 0) {
+                rc = gemm_update(c, ss, Wb + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                                 tc ? lah + (size_t)l0 * NB + r : nullptr, tc ? lal + (size_t)l0 * NB + r : nullptr,
                                  tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
-                                 P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
+                                 Wb + kk + kNb, m, nin, kNb);
                 if (rc) return rc;
             }
         }
-        const float* P0 = P + k0;
-        PanelRef pr{P0, ld, P0 + kb, ld, ubh, ubl};
-        if (fork) {
-            CK(cudaEventRecord(c->ev_side, ss));
-            CK(cudaStreamWaitEvent(s, c->ev_side, 0));
-        } else if ((rc = col_panel(c, K, pr, l0, sb))) return rc;
-        if ((rc = trailing_update(c, K, pr, sb, l0, c->rows_local))) return rc;
+        const int mrem = kb - (r + kNb);
+        if (mrem > 0) {
+            launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
+                        tc ? lah + (size_t)(k0 + r + kNb) * NB : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB : nullptr, NB, r, s);
+            rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                             tc ? lah + (size_t)(k0 + r + kNb) * NB + r : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB + r : nullptr,
+                             tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
+                             P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
+            if (rc) return rc;
+        }
     }
+    const float* P0 = P + k0;
+    PanelRef pr{P0, ld, P0 + kb, ld, ubh, ubl};
+    if (fork) {
+        CK(cudaEventRecord(c->ev_side, ss));
+        CK(cudaStreamWaitEvent(s, c->ev_side, 0));
+    } else if ((rc = col_panel(c, K, pr, l0, sb, row_hi))) return rc;
+    return trailing_update(c, K, pr, sb, l0, row_hi);
+}
+
+static int factor_single(gauss_cuda_ctx* c)
+{
+    for (int K = 0; K < c->nblk; ++K) {
+        int rc = outer_step(c, K, c->rows_local, c->ub_hi[0], c->ub_lo[0]);
+        if (rc) return rc;
+    }
+    return GAUSS_CUDA_OK;
+}
+
+// Single GPU, host-resident input: elimination overlapped with the upload.  The rows arrive in chunks of whole
+// outer blocks on a copy stream.  A chunk is first brought up to date with every panel factored before it arrived
+// (L-col solve + trailing update restricted to the chunk's rows: the up-looking half), then its own outer blocks
+// are factored right-looking with the rows below limited to the chunk.  Every element receives the same rank-NB
+// updates in the same order through the same tiles as in factor_single, so the result is bit-identical; what
+// changes is that only the first chunk's transfer is exposed.  The split U operand of every panel stays resident
+// (2 x ld x np floats) because later chunks need all of them.
+static int factor_streamed(gauss_cuda_ctx* c, const float* A, const float* B)
+{
+    cudaStream_t s = c->s_main, sc = c->s_copy;
+    const int NB = c->NB, ld = c->ld, n = c->n;
+    const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
+    const size_t ubsz = (size_t)ld * NB;
+    // Chunk boundaries in outer blocks.  Early rows carry little work (row r receives r panels' updates) and every
+    // chunk pays a latency-bound L-col chain per panel factored before it, so the chunks start small -- little
+    // transfer exposed, few earlier panels -- and grow towards the end, where the elimination is far behind the
+    // copy stream anyway.  (N = 32768 on B200, measured: 4 equal chunks 160 ms, 8 equal 163 ms, 16 equal 184 ms.)
+    std::vector<int> bound;
+    if (c->stream_chunks > 0) {
+        const int nchunks = std::min(c->stream_chunks, c->nblk), cblk = (c->nblk + nchunks - 1) / nchunks;
+        for (int b = cblk; b < c->nblk; b += cblk) bound.push_back(b);
+    } else {
+        static const int frac32[] = {1, 3, 5, 7, 9, 11, 14, 20};
+        for (int f : frac32) {
+            const int b = (f * c->nblk + 16) / 32;
+            if (b > 0 && b < c->nblk && (bound.empty() || b > bound.back())) bound.push_back(b);
+        }
+    }
+    bound.push_back(c->nblk);
+    const int nchunks = (int)bound.size();
+    const StepBufs sb{s, c->la_hi[0], c->la_lo[0]};
+    CK(cudaMemsetAsync(c->status, 0, sizeof(int), s));
+    c->bcast_bytes = 0.0;
+    c->upd_count = 0;
+    CK(cudaEventRecord(c->ev_gate, s));                        // the copy stream must not overtake earlier work on W
+    CK(cudaStreamWaitEvent(sc, c->ev_gate, 0));
+    CK(cudaMemcpyAsync(c->hvec, B, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, sc));
+    // chunk ci+1 is handed to the copy stream before the kernels of chunk ci are launched: with pinned host memory
+    // all of it is asynchronous anyway; with pageable memory the host blocks in the copy while the GPU works
+    auto send_chunk = [&](int ci) -> int {
+        if (ci >= nchunks) return GAUSS_CUDA_OK;
+        const int R0 = ci ? bound[ci - 1] : 0, R1 = bound[ci];
+        int rc = upload_blocks(c, c->W, A, R0, R1, sc);
+        if (rc) return rc;
+        CK(cudaEventRecord(c->ev_chunk[ci], sc));
+        if (R1 == c->nblk) CK(cudaEventRecord(c->ev_h2d_done, sc));
+        return GAUSS_CUDA_OK;
+    };
+    { int rc = send_chunk(0); if (rc) return rc; }
+    for (int ci = 0; ci < nchunks; ++ci) {
+        const int R0 = ci ? bound[ci - 1] : 0, R1 = bound[ci];
+        const int r0 = R0 * NB, r1 = std::min(R1 * NB, c->np);
+        { int rc = send_chunk(ci + 1); if (rc) return rc; }
+        CK(cudaStreamWaitEvent(s, c->ev_chunk[ci], 0));
+        int rc;
+        for (int K = 0; K < R0; ++K) {                         // panels factored before this chunk arrived
+            const int k0 = K * NB, kb = blk_rows(c, K);
+            const float* P0 = c->W + (size_t)k0 * ld + k0;
+            PanelRef pr{P0, ld, P0 + kb, ld, tc ? c->ub_all_hi + K * ubsz : nullptr, tc ? c->ub_all_lo + K * ubsz : nullptr};
+            if ((rc = col_panel(c, K, pr, r0, sb, r1))) return rc;
+            if ((rc = trailing_update(c, K, pr, sb, r0, r1))) return rc;
+        }
+        for (int K = R0; K < R1; ++K)
+            if ((rc = outer_step(c, K, r1, tc ? c->ub_all_hi + K * ubsz : nullptr, tc ? c->ub_all_lo + K * ubsz : nullptr))) return rc;
+    }
+    CK(cudaGetLastError());
+    c->factored = true;
     return GAUSS_CUDA_OK;
 }
 
@@ -843,6 +943,11 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
     gauss_cuda_stats& o = c->last;
     auto el = [&](int a, int b) { float ms = 0.f; cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]); return (double)ms * 1e-3; };
     o.h2d_s = h2d ? el(0, 1) : 0.0;
+    if (h2d && c->last_streamed) {             // overlapped schedule: the upload runs beside the elimination
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c->ev[0], c->ev_h2d_done) == cudaSuccess) o.h2d_s = (double)ms * 1e-3;
+    }
+    o.overlapped_upload = c->last_streamed ? 1 : 0;
     o.factor_s = fac ? el(1, 2) : 0.0;
     o.backsub_s = bs ? el(2, 3) : 0.0;
     o.d2h_s = d2h ? el(3, 4) : 0.0;
@@ -960,6 +1065,25 @@ static int run_core(gauss_cuda_ctx* c)
     return core_body(c);
 }
 
+// Streams, events and the resident split-U buffers of the overlapped schedule, on first use.
+static int stream_setup(gauss_cuda_ctx* c)
+{
+    if (c->s_copy) return GAUSS_CUDA_OK;
+    CK(cudaStreamCreateWithFlags(&c->s_copy, cudaStreamNonBlocking));
+    c->ev_chunk.assign((size_t)c->nblk, nullptr);
+    for (auto& e : c->ev_chunk) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&c->ev_gate, cudaEventDisableTiming));
+    CK(cudaEventCreate(&c->ev_h2d_done));
+    if (c->mode == GAUSS_CUDA_MODE_3XTF32) {
+        const size_t bytes = (size_t)c->nblk * c->ld * c->NB * sizeof(float);
+        CK(cudaMalloc((void**)&c->ub_all_hi, bytes));
+        CK(cudaMalloc((void**)&c->ub_all_lo, bytes));
+        CK(cudaMemset(c->ub_all_hi, 0, bytes));
+        CK(cudaMemset(c->ub_all_lo, 0, bytes));
+    }
+    return GAUSS_CUDA_OK;
+}
+
 extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* B, float* X, float* B_out, gauss_cuda_stats* st)
 {
     if (!c || !A || !B || !X) return GAUSS_CUDA_BAD_ARG;
@@ -967,12 +1091,25 @@ extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* 
     g_launch_count = 0;
     cudaStream_t s = c->s_main;
     int rc;
+    c->last_streamed = c->world == 1 && !c->pivot && c->stream_on && c->np >= c->stream_min_n && c->nblk >= 2;
+    if (c->last_streamed && (rc = stream_setup(c))) return rc;
     CK(cudaEventRecord(c->ev[0], s));
-    if ((rc = upload_into(c, c->W, A, B))) return rc;
-    if ((rc = run_core(c))) return rc;
+    if (c->last_streamed) {
+        CK(cudaEventRecord(c->ev[1], s));
+        if ((rc = factor_streamed(c, A, B))) return rc;
+        CK(cudaEventRecord(c->ev[2], s));
+        if ((rc = snapshot_rhs(c))) return rc;
+        if ((rc = backsub(c))) return rc;
+        CK(cudaEventRecord(c->ev[3], s));
+    } else {
+        if ((rc = upload_into(c, c->W, A, B))) return rc;
+        if ((rc = run_core(c))) return rc;
+    }
     if ((rc = download_results(c, X, B_out))) return rc;
     CK(cudaEventRecord(c->ev[4], s));
-    return finish_stats(c, st, true, true, true, true);
+    rc = finish_stats(c, st, true, true, true, true);
+    c->last_streamed = false;
+    return rc;
 }
 
 extern "C" int gauss_cuda_upload(gauss_cuda_ctx* c, const float* A, const float* B)

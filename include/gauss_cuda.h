@@ -56,6 +56,11 @@ typedef struct {
      * events on the library's stream: summed duration, algorithmic flops (2*m*n*k per launch), launches */
     double update_s, update_flops;
     int    update_launches;
+    /* 1: gauss_cuda_solve ran the overlapped schedule (rows uploaded in chunks beside the elimination; single
+     * GPU, n >= 16384 unless GAUSS_CUDA_STREAM / GAUSS_CUDA_STREAM_MIN_N / GAUSS_CUDA_STREAM_CHUNKS say
+     * otherwise).  h2d_s is then the time until the last chunk had arrived and factor_s (which contains the
+     * waiting for chunks) overlaps it; results are bit-identical to the upload-first schedule. */
+    int    overlapped_upload;
 } gauss_cuda_stats;
 
 /* ---- Gaussian elimination ------------------------------------------------------------- */

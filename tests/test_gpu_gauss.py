@@ -123,6 +123,46 @@ def test_zero_pivot_reported_as_singular(mode):
 
 
 @pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n,nb,chunks", [(2100, 256, 3), (1500, 128, 8), (2048, 512, 2), (1100, 256, 64), (2100, 128, 0), (4000, 128, 0)])
+def test_overlapped_upload_is_bit_identical(n, nb, chunks, mode, monkeypatch):
+    # gauss_cuda_solve on a single GPU uploads the rows in chunks beside the elimination (by default from n = 16384;
+    # forced here): every element must see the same updates in the same order as in the upload-first schedule
+    A, B, Xtrue = pkg.initialize_inputs(n, 4)
+    monkeypatch.setenv("GAUSS_CUDA_STREAM_MIN_N", "0")
+    if chunks:                                 # 0: the default graded schedule (small chunks first)
+        monkeypatch.setenv("GAUSS_CUDA_STREAM_CHUNKS", str(chunks))
+    with pkg.GaussCuda(n, mode=mode, nb=nb) as g:
+        X1, B1 = g.gauss(A, B, want_b_after=True)
+        assert g.stats.overlapped_upload == 1
+        LU1 = g.download_factors()
+        X1b = g.gauss(A, B)                    # and again on the same context
+        g.upload(A, B)
+        g.solve_resident()
+        assert g.stats.overlapped_upload == 0
+        X2, B2 = g.download(want_b_after=True)
+        LU2 = g.download_factors()
+    monkeypatch.setenv("GAUSS_CUDA_STREAM", "0")
+    with pkg.GaussCuda(n, mode=mode, nb=nb) as g:
+        X3 = g.gauss(A, B)
+        assert g.stats.overlapped_upload == 0
+    assert ol.max_rel_error(X1, Xtrue) <= TOL
+    assert np.array_equal(LU1, LU2)
+    assert np.array_equal(X1, X2) and np.array_equal(X1, X1b) and np.array_equal(X1, X3) and np.array_equal(B1, B2)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_overlapped_upload_reports_singular(mode, monkeypatch):
+    monkeypatch.setenv("GAUSS_CUDA_STREAM_MIN_N", "0")
+    n = 1000
+    A, B, _ = pkg.initialize_inputs(n, 3)
+    A[600:, :601] = 0.0                         # rows >= 600 are untouched by the first 600 steps and start with a zero
+    with pkg.GaussCuda(n, mode=mode, nb=256) as g:
+        with pytest.raises(pkg.SingularMatrix):
+            g.gauss(A, B)
+        assert g.stats.zero_pivot_row == 600 and g.stats.overlapped_upload == 1
+
+
+@pytest.mark.parametrize("mode", MODES)
 def test_resident_api_equals_host_api(mode):
     n = 700
     A, B, _ = pkg.initialize_inputs(n, 8)
