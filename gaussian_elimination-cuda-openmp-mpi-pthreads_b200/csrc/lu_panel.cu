@@ -10,6 +10,7 @@
 // urow/lcol invert the four 32x32 diagonal sub-blocks once per CTA (one warp each) and then run
 // block forward substitution:  X_b = inv(D_b) * (A_b - sum_{c<b} L_bc X_c)  as dense products.
 #include "gauss_internal.cuh"
+#include <type_traits>
 
 namespace gb200 {
 
@@ -390,11 +391,23 @@ urow_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int
     }
 }
 
+// 3xTF32 mode runs the tensor-core variants (section 4) unless GAUSS_CUDA_PANEL_MMA=0; the FFMA mode keeps the
+// pure-FP32 kernels above
+static int g_panel_mma = -1;
+static bool panel_mma_enabled()
+{
+    if (g_panel_mma < 0) { const char* e = getenv("GAUSS_CUDA_PANEL_MMA"); g_panel_mma = (e && atoi(e) == 0) ? 0 : 1; }
+    return g_panel_mma != 0;
+}
+static void launch_urow_mma(const float* l11, int ldl, float* a12, int ld, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s);
+static void launch_lcol_mma(const float* u11, int ldu, float* a21, int ld, int nrows, float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s);
+
 void launch_urow(const float* l11, int ldl, float* a12, int ld, int ncols,
                  float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s)
 {
     if (ncols <= 0) return;
-    urow_kernel<<<(ncols + UW - 1) / UW, 256, sizeof(UrowSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
+    if (ub_hi != nullptr && panel_mma_enabled()) launch_urow_mma(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub, s);
+    else urow_kernel<<<(ncols + UW - 1) / UW, 256, sizeof(UrowSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
     ++g_launch_count;
 }
 
@@ -513,12 +526,286 @@ void launch_lcol(const float* u11, int ldu, float* a21, int ld, int nrows,
                  float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s)
 {
     if (nrows <= 0) return;
-    lcol_kernel<<<(nrows + LH - 1) / LH, 256, sizeof(LcolSmem), s>>>(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
+    if (la_hi != nullptr && panel_mma_enabled()) launch_lcol_mma(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la, s);
+    else lcol_kernel<<<(nrows + LH - 1) / LH, 256, sizeof(LcolSmem), s>>>(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
     ++g_launch_count;
+}
+
+// =====================================================================================
+// 4. The two panel solves on the tensor cores (3xTF32 mode).
+//    Both are the same computation: four 32-wide stages of  X_b = inv(D_bb) S_b  followed by
+//    S_s -= O_sb X_b  for the later sub-blocks s > b, where the right-hand sides -- matrix columns for
+//    the U-row solve, matrix rows for the L-col solve -- never interact.  A warp therefore owns 8 of them
+//    for the whole solve and keeps all 128 x 8 values in mma accumulator registers; there is no
+//    block-wide barrier between the stages.  The products run as warp-level m16n8k8 TF32 MMAs
+//    (mma.sync: these are 32 x 32 x 8 products, far below a tcgen05 tile) with the same 3xTF32 split
+//    as the trailing update -- lo*hi + hi*lo + hi*hi into an FP32 accumulator.  X_b goes through the
+//    warp's own columns of the shared-memory strip to change from accumulator layout to B-operand layout.
+//    Template strides: the constant operand element (m, k) is at A[m*SAM + k*SAK], the data element
+//    (i, n) at D[i*SDI + n*SDN]  (i = index along the solve, n = which of the warp's 8 right-hand sides).
+// =====================================================================================
+// Operand split for the MMAs below: hi = x truncated to TF32 (the tensor core ignores the low 13 bits anyway),
+// lo = x - hi (exact in FP32), truncated likewise.  Three ALU instructions; cvt.rna.tf32 is emulated in ~4 each
+// on sm_100 and these kernels split every operand on the fly.  The representation error is <= 2^-21 |x|, the
+// same order as the lo*lo term 3xTF32 drops.
+template <uint32_t SIGN = 0u>                              // SIGN = 0x80000000: the split of -x
+__device__ __forceinline__ void split_bits(const float x, uint32_t& hi, uint32_t& lo)
+{
+    const uint32_t h = __float_as_uint(x) & 0xffffe000u;
+    hi = h ^ SIGN;
+    lo = (__float_as_uint(x - __uint_as_float(h)) & 0xffffe000u) ^ SIGN;
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2])
+{
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+template <int SAM, int SAK, int SDI, int SDN, int BLK>
+__device__ __forceinline__ void tri_blocks_mma(const float* __restrict__ inv, const float* __restrict__ off,
+                                               float* __restrict__ D, const int lane)
+{
+    const int g = lane >> 2, t = lane & 3;
+    float acc[8][4];
+#pragma unroll
+    for (int M = 0; M < 8; ++M) {
+        acc[M][0] = D[(16 * M + g) * SDI + (2 * t) * SDN];
+        acc[M][1] = D[(16 * M + g) * SDI + (2 * t + 1) * SDN];
+        acc[M][2] = D[(16 * M + g + 8) * SDI + (2 * t) * SDN];
+        acc[M][3] = D[(16 * M + g + 8) * SDI + (2 * t + 1) * SDN];
+    }
+    auto store_sub = [&](const int b) {                    // sub-block b of the warp's right-hand sides -> D
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            const int M = 2 * b + mt;
+            D[(16 * M + g) * SDI + (2 * t) * SDN] = acc[M][0];
+            D[(16 * M + g) * SDI + (2 * t + 1) * SDN] = acc[M][1];
+            D[(16 * M + g + 8) * SDI + (2 * t) * SDN] = acc[M][2];
+            D[(16 * M + g + 8) * SDI + (2 * t + 1) * SDN] = acc[M][3];
+        }
+    };
+    auto load_b = [&](const int b, uint32_t (&bh)[4][2], uint32_t (&bl)[4][2]) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+            split_bits(D[(32 * b + 8 * ks + t) * SDI + g * SDN], bh[ks][0], bl[ks][0]);
+            split_bits(D[(32 * b + 8 * ks + t + 4) * SDI + g * SDN], bh[ks][1], bl[ks][1]);
+        }
+    };
+    auto mac_tile = [&](float (&d)[4], const float* __restrict__ A, const int mt, auto neg,
+                        const uint32_t (&bh)[4][2], const uint32_t (&bl)[4][2]) {
+        constexpr uint32_t SG = decltype(neg)::value ? 0x80000000u : 0u;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+            uint32_t ah[4], al[4];
+            split_bits<SG>(A[(16 * mt + g) * SAM + (8 * ks + t) * SAK], ah[0], al[0]);
+            split_bits<SG>(A[(16 * mt + g + 8) * SAM + (8 * ks + t) * SAK], ah[1], al[1]);
+            split_bits<SG>(A[(16 * mt + g) * SAM + (8 * ks + t + 4) * SAK], ah[2], al[2]);
+            split_bits<SG>(A[(16 * mt + g + 8) * SAM + (8 * ks + t + 4) * SAK], ah[3], al[3]);
+            mma_tf32(d, al, bh[ks]);
+            mma_tf32(d, ah, bl[ks]);
+            mma_tf32(d, ah, bh[ks]);
+        }
+    };
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+        uint32_t bh[4][2], bl[4][2];
+        if (b > 0) { store_sub(b); __syncwarp(); }          // S_b with the updates of the earlier stages
+        load_b(b, bh, bl);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {                     // X_b = inv(D_bb) S_b
+            float d[4] = {0.f, 0.f, 0.f, 0.f};
+            mac_tile(d, inv + b * BLK, mt, std::false_type{}, bh, bl);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[2 * b + mt][e] = d[e];
+        }
+        __syncwarp();
+        store_sub(b);
+        __syncwarp();
+        if (b < 3) {
+            load_b(b, bh, bl);                               // X_b as the B operand
+#pragma unroll
+            for (int s_ = b + 1; s_ < 4; ++s_)               // S_s -= O_sb X_b
+#pragma unroll
+                for (int mt = 0; mt < 2; ++mt)
+                    mac_tile(acc[2 * s_ + mt], off + (s_ * (s_ - 1) / 2 + b) * BLK, mt, std::true_type{}, bh, bl);
+        }
+    }
+}
+
+// (s, b) of the off-diagonal sub-block with id = s (s - 1) / 2 + b, s > b
+__device__ __forceinline__ void offdiag_pair(const int id, int& s_, int& b)
+{
+    s_ = id < 1 ? 1 : (id < 3 ? 2 : 3);
+    b = id - s_ * (s_ - 1) / 2;
+}
+
+constexpr int kUP = 36;                  // pitch of the 32 x 32 blocks of L11 (conflict-free A fragments: 4g + t)
+constexpr int kUS = UW + 8;              // pitch of the strip (conflict-free B fragments: 8t + g)
+struct UrowMmaSmem {
+    float Ld[4][32][kUP];                // diagonal sub-blocks of L11
+    float Lo[6][32][kUP];                // sub-blocks (s, b), s > b
+    float inv[4][32][kUP];               // inverses of the diagonal sub-blocks
+    float strip[kNb][kUS];
+};
+
+__global__ void __launch_bounds__(256, 2)
+urow_mma_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int ld, int ncols,
+                float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    UrowMmaSmem& sm = *reinterpret_cast<UrowMmaSmem*>(smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int c0 = blockIdx.x * UW;
+
+    for (int idx = tid; idx < 4 * 32 * 8; idx += 256) {
+        const int bb = idx >> 8, r = (idx >> 3) & 31, c4 = (idx & 7) << 2;
+        cp_async16(&sm.Ld[bb][r][c4], l11 + (size_t)(32 * bb + r) * ldl + 32 * bb + c4);
+    }
+    cp_async_commit();
+    for (int idx = tid; idx < 6 * 32 * 8; idx += 256) {
+        const int id = idx >> 8, r = (idx >> 3) & 31, c4 = (idx & 7) << 2;
+        int s_, b;
+        offdiag_pair(id, s_, b);
+        cp_async16(&sm.Lo[id][r][c4], l11 + (size_t)(32 * s_ + r) * ldl + 32 * b + c4);
+    }
+    {
+        const int c4 = (tid & 15) << 2;
+        const bool ok = c0 + c4 < ncols;
+        for (int r = tid >> 4; r < kNb; r += 16) {
+            if (ok) cp_async16(&sm.strip[r][c4], a12 + (size_t)r * ld + c0 + c4);
+            else *reinterpret_cast<float4*>(&sm.strip[r][c4]) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    }
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();
+    if (warp < 4) {                                        // inverse of the lower-triangular sub-block `warp`
+        const float myrinv = 1.0f / sm.Ld[warp][lane][lane];
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = (i == lane) ? 1.f : 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            x[j] *= __shfl_sync(0xffffffffu, myrinv, j);
+#pragma unroll
+            for (int i = j + 1; i < 32; ++i) x[i] = fmaf(-sm.Ld[warp][i][j], x[j], x[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sm.inv[warp][i][lane] = x[i];
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+
+    tri_blocks_mma<kUP, 1, kUS, 1, 32 * kUP>(&sm.inv[0][0][0], &sm.Lo[0][0][0], &sm.strip[0][8 * warp], lane);
+    __syncthreads();
+
+    {
+        const int c4 = (tid & 15) << 2;
+        if (c0 + c4 < ncols)
+            for (int r = tid >> 4; r < kNb; r += 16)
+                *reinterpret_cast<float4*>(a12 + (size_t)r * ld + c0 + c4) = *reinterpret_cast<const float4*>(&sm.strip[r][c4]);
+    }
+    if (ub_hi != nullptr) {
+        const int c = tid & 63, part = tid >> 6;           // 4 threads per column, 32 rows each
+        if (c0 + c < ncols) {
+            float* dh = ub_hi + (size_t)(c0 + c) * ldub + k_ub + 32 * part;
+            float* dl = ub_lo + (size_t)(c0 + c) * ldub + k_ub + 32 * part;
+#pragma unroll 2
+            for (int r = 0; r < 32; r += 4) {
+                float4 h, l;
+                tf32_split2(sm.strip[32 * part + r][c], h.x, l.x);
+                tf32_split2(sm.strip[32 * part + r + 1][c], h.y, l.y);
+                tf32_split2(sm.strip[32 * part + r + 2][c], h.z, l.z);
+                tf32_split2(sm.strip[32 * part + r + 3][c], h.w, l.w);
+                *reinterpret_cast<float4*>(dh + r) = h;
+                *reinterpret_cast<float4*>(dl + r) = l;
+            }
+        }
+    }
+}
+
+constexpr int kLP = 40;                  // pitch of the 32 x 32 blocks of U11 (transposed A fragments: 8t + g)
+constexpr int kLS = kNb + 4;             // pitch of the row tile (B fragments: 4g + t)
+struct LcolMmaSmem {
+    float Ud[4][32][kLP];                // diagonal sub-blocks of U11 (unit diagonal implied)
+    float Uo[6][32][kLP];                // sub-blocks (rows of b, columns of s), s > b
+    float inv[4][32][kLP];
+    float tile[LH][kLS];
+};
+
+__global__ void __launch_bounds__(256, 2)
+lcol_mma_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int ld, int nrows,
+                float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    LcolMmaSmem& sm = *reinterpret_cast<LcolMmaSmem*>(smem_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int row0 = blockIdx.x * LH;
+
+    for (int idx = tid; idx < 4 * 32 * 8; idx += 256) {
+        const int bb = idx >> 8, r = (idx >> 3) & 31, c4 = (idx & 7) << 2;
+        cp_async16(&sm.Ud[bb][r][c4], u11 + (size_t)(32 * bb + r) * ldu + 32 * bb + c4);
+    }
+    cp_async_commit();
+    for (int idx = tid; idx < 6 * 32 * 8; idx += 256) {
+        const int id = idx >> 8, r = (idx >> 3) & 31, c4 = (idx & 7) << 2;
+        int s_, b;
+        offdiag_pair(id, s_, b);
+        cp_async16(&sm.Uo[id][r][c4], u11 + (size_t)(32 * b + r) * ldu + 32 * s_ + c4);
+    }
+    for (int r = warp; r < LH; r += 8) {
+        if (row0 + r < nrows) cp_async16(&sm.tile[r][4 * lane], a21 + (size_t)(row0 + r) * ld + 4 * lane);
+        else *reinterpret_cast<float4*>(&sm.tile[r][4 * lane]) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    cp_async_commit();
+    cp_async_wait<1>();
+    __syncthreads();
+    if (warp < 4) {                                        // inverse of the unit-upper sub-block `warp`
+        float x[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = (i == lane) ? 1.f : 0.f;
+#pragma unroll
+        for (int j = 31; j > 0; --j) {
+#pragma unroll
+            for (int i = 0; i < j; ++i) x[i] = fmaf(-sm.Ud[warp][i][j], x[j], x[i]);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) sm.inv[warp][i][lane] = x[i];
+    }
+    cp_async_wait<0>();
+    __syncthreads();
+
+    // transposed roles: X_b = S_b inv(U_bb) is  X_b^T = inv(U_bb)^T S_b^T, the constant operand is read transposed
+    tri_blocks_mma<1, kLP, 1, kLS, 32 * kLP>(&sm.inv[0][0][0], &sm.Uo[0][0][0], &sm.tile[8 * warp][0], lane);
+    __syncthreads();
+
+    for (int r = warp; r < LH; r += 8) {
+        if (row0 + r >= nrows) break;
+        const float4 v = *reinterpret_cast<const float4*>(&sm.tile[r][4 * lane]);
+        *reinterpret_cast<float4*>(a21 + (size_t)(row0 + r) * ld + 4 * lane) = v;
+        if (la_hi != nullptr) {
+            float4 h, l;
+            tf32_split2(v.x, h.x, l.x); tf32_split2(v.y, h.y, l.y); tf32_split2(v.z, h.z, l.z); tf32_split2(v.w, h.w, l.w);
+            *reinterpret_cast<float4*>(la_hi + (size_t)(row0 + r) * ldla + k_la + 4 * lane) = h;
+            *reinterpret_cast<float4*>(la_lo + (size_t)(row0 + r) * ldla + k_la + 4 * lane) = l;
+        }
+    }
+}
+
+static void launch_urow_mma(const float* l11, int ldl, float* a12, int ld, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s)
+{
+    urow_mma_kernel<<<(ncols + UW - 1) / UW, 256, sizeof(UrowMmaSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
+}
+static void launch_lcol_mma(const float* u11, int ldu, float* a21, int ld, int nrows, float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s)
+{
+    lcol_mma_kernel<<<(nrows + LH - 1) / LH, 256, sizeof(LcolMmaSmem), s>>>(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
 }
 
 void panel_setup_device()
 {
+    cudaFuncSetAttribute(urow_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowMmaSmem));
+    cudaFuncSetAttribute(lcol_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolMmaSmem));
     cudaFuncSetAttribute(urow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowSmem));
     cudaFuncSetAttribute(lcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolSmem));
 }
