@@ -427,6 +427,7 @@ static int gemm_update(gauss_cuda_ctx* c, cudaStream_t s, const float* A, int ld
     }
     tc_set_sched_slots(c->sched);
     tc_set_max_tiles(max_tiles);
+    tc_set_pair_ok(c->world == 1);             // multi-GPU steps share SMs with NCCL: they need the dynamic scheduler
     int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, s);
     tc_set_max_tiles(0);
     tc_set_sched_slots(nullptr);

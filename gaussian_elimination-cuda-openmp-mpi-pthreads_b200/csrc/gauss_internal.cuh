@@ -78,6 +78,7 @@ bool tc_available();
 // Scheduler slots (2 * 64 zeroed ints of device memory) used by this thread's following tc_gemm_nt calls;
 // nullptr = the library's own ring.
 void tc_set_sched_slots(int* slots);
+void tc_set_pair_ok(bool ok);       // false: this thread's launches must use the dynamic-scheduler kernel (multi-GPU)
 // > 0: CTAs of this thread's following tc_gemm_nt launches exit after that many tiles (the grid grows to match),
 // so kernels of other streams get SMs while a long launch runs.  0 = persistent CTAs.
 void tc_set_max_tiles(int max_tiles);

@@ -18,6 +18,7 @@
 
 #include <cuda.h>
 #include <stdio.h>
+#include <algorithm>
 
 namespace gb200 {
 
@@ -345,6 +346,232 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
     }
 }
 
+// ---------------------------------------------------------------------------- the CTA-pair kernel
+// Same pipeline with tcgen05.mma.cta_group::2: the two CTAs of a cluster (one TPC) compute a 256 x 256 tile.
+// Each CTA stages its own 128 rows of A and HALF of the B tile (128 of the 256 columns); the MMA, issued by
+// one thread of the even CTA, reads both halves across the pair and accumulates rows 0..127 / 128..255 into the
+// two CTAs' own TMEM.  Per CTA and k-slice that is 64 KB through TMA instead of 96 KB -- the L2 -> SM stream is
+// what keeps the single-CTA kernel at ~80 % tensor-pipe utilisation -- and the smaller stage buys a third
+// pipeline stage.  Hand-offs:
+//   full[s]    (even CTA only)  expect_tx by the even producer for BOTH CTAs' bytes; both producers' TMA loads
+//                               signal it (mbarrier address with the peer bit cleared)
+//   empty[s]   (both)           tcgen05.commit ... multicast to both CTAs
+//   tfull[a]   (both)           tcgen05.commit ... multicast: accumulator `a` complete
+//   tempty[a]  (even CTA only)  256 arrivals: the 128 epilogue threads of each CTA (the odd CTA's arrive remotely)
+// Tiles are assigned round-robin to the pairs (both CTAs derive the same sequence; no queue).  Each output element
+// sees the same MMAs in the same order as in the single-CTA kernel, so results are bit-identical.
+constexpr int TBM2 = 256;
+constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;            // shared::cluster address -> the even CTA of the pair
+
+template <int BK, int STAGES>
+struct TcCfg2 {
+    static constexpr int a_bytes = TBM * BK * 4;           // this CTA's 128 rows of A
+    static constexpr int b_bytes = (TBN / 2) * BK * 4;     // this CTA's half of B
+    static constexpr int stage_bytes = 2 * a_bytes + 2 * b_bytes;
+    static constexpr int ring_bytes = STAGES * stage_bytes;
+    static constexpr int bar_off = ring_bytes + 2 * TSTAGE_C;
+    static constexpr int smem_bytes = bar_off + 256 + 1024;
+    static constexpr int swizzle_bytes = BK * 4;
+};
+
+__device__ __forceinline__ uint32_t cluster_ctarank()
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all()
+{
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair(const CUtensorMap* map, uint32_t bar_even, uint32_t dst, int c0, int c1)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar_even), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_even(uint32_t bar)        // arrive on the even CTA's copy of `bar`
+{
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar)        // arrives on `bar` in both CTAs
+{
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+
+__device__ __forceinline__ void tile_coords2(int t, int num_m, int num_n, int& m0, int& n0)
+{
+    const int band_tiles = num_m * kBandN;
+    const int band = t / band_tiles;
+    const int in_band = t - band * band_tiles;
+    const int wb = min(kBandN, num_n - band * kBandN);
+    const int mi = in_band / wb;
+    const int ni = band * kBandN + (in_band - mi * wb);
+    m0 = mi * TBM2;
+    n0 = ni * TBN;
+}
+
+template <int BK, int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
+tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant__ CUtensorMap tm_alo,
+                    const __grid_constant__ CUtensorMap tm_bhi, const __grid_constant__ CUtensorMap tm_blo,
+                    const __grid_constant__ CUtensorMap tm_c,
+                    int m, int n, int k, int negate, int reduce)
+{
+    using Cfg = TcCfg2<BK, STAGES>;
+    extern __shared__ unsigned char smem_dyn[];
+    const uint32_t base = (smem_u32(smem_dyn) + 1023u) & ~1023u;
+    const uint32_t bar_base = base + Cfg::bar_off;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+    auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+    const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    unsigned char* gen_base = smem_dyn + (base - smem_u32(smem_dyn));
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();                // 0: even CTA (issues the MMAs), 1: its peer
+    const int pair = (int)blockIdx.x >> 1, num_pairs = (int)gridDim.x >> 1;
+    const int num_n = (n + TBN - 1) / TBN;
+    const int num_m = (m + TBM2 - 1) / TBM2;
+    const int num_tiles = num_m * num_n;
+    const int num_kb = k / BK;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 256); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {                                        // both CTAs, same warp: the pair allocates together
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync_all();                                     // barriers of both CTAs initialised before anyone signals them
+    tc_fence_after();
+    const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 4));
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (elect_one()) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs) {
+                int m0, n0;
+                tile_coords2(t, num_m, num_n, m0, n0);
+                const int am = m0 + (int)rank * TBM, bn = n0 + (int)rank * (TBN / 2);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(empty_bar(stage), phase ^ 1);
+                    const uint32_t sa = base + stage * Cfg::stage_bytes;
+                    const uint32_t fb = full_bar(stage) & kPeerBitMask;
+                    if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * Cfg::stage_bytes);
+                    tma_load_2d_pair(&tm_ahi, fb, sa, kb * BK, am);
+                    tma_load_2d_pair(&tm_alo, fb, sa + Cfg::a_bytes, kb * BK, am);
+                    tma_load_2d_pair(&tm_bhi, fb, sa + 2 * Cfg::a_bytes, kb * BK, bn);
+                    tma_load_2d_pair(&tm_blo, fb, sa + 2 * Cfg::a_bytes + Cfg::b_bytes, kb * BK, bn);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (even CTA only) =====================
+        if (rank == 0 && elect_one()) {
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((negate ? 1u : 0u) << 13) |
+                                   ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM2 >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            int it = 0;
+            for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+                const int as = it & 1;
+                const uint32_t aphase = (it >> 1) & 1;
+                mbar_wait(tempty_bar(as), aphase ^ 1);
+                tc_fence_after();
+                const uint32_t tacc = tmem_base + (uint32_t)(as * TBN);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(full_bar(stage), phase);
+                    tc_fence_after();
+                    const uint32_t sa = base + stage * Cfg::stage_bytes;
+                    const uint64_t d_ahi = make_kmajor_desc<Cfg::swizzle_bytes>(sa);
+                    const uint64_t d_alo = make_kmajor_desc<Cfg::swizzle_bytes>(sa + Cfg::a_bytes);
+                    const uint64_t d_bhi = make_kmajor_desc<Cfg::swizzle_bytes>(sa + 2 * Cfg::a_bytes);
+                    const uint64_t d_blo = make_kmajor_desc<Cfg::swizzle_bytes>(sa + 2 * Cfg::a_bytes + Cfg::b_bytes);
+#pragma unroll
+                    for (int kk = 0; kk < BK / 8; ++kk) {
+                        const uint64_t adv = (uint64_t)((kk * 32) >> 4);
+                        umma_tf32_pair(tacc, d_alo + adv, d_bhi + adv, idesc, (kb | kk) ? 1u : 0u);
+                        umma_tf32_pair(tacc, d_ahi + adv, d_blo + adv, idesc, 1u);
+                        umma_tf32_pair(tacc, d_ahi + adv, d_bhi + adv, idesc, 1u);
+                    }
+                    umma_commit_pair(empty_bar(stage));
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                umma_commit_pair(tfull_bar(as));
+            }
+        }
+    } else {
+        // ===================== epilogue (warps 2..5 of both CTAs: each CTA drains its own 128 rows) =====================
+        const int q = warp & 3;
+        const int row = q * 32 + lane;
+        const bool issuer = (threadIdx.x == 64);
+        int cbuf = 0;
+        int it = 0;
+        for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+            int m0, n0;
+            tile_coords2(t, num_m, num_n, m0, n0);
+            m0 += (int)rank * TBM;
+            const int as = it & 1;
+            const uint32_t aphase = (it >> 1) & 1;
+            mbar_wait(tfull_bar(as), aphase);
+            tc_fence_after();
+            const int nchunks = min(TBN / TEPI_W, (n - n0 + TEPI_W - 1) / TEPI_W);
+            const bool live = m0 < m;                       // the odd CTA of the last tile row may hold no rows
+            for (int c = 0; c < nchunks; ++c) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TBN + c * TEPI_W), v);
+                tmem_ld_wait();
+                if (c == nchunks - 1) {
+                    tc_fence_before();
+                    mbar_arrive_even(tempty_bar(as));
+                }
+                if (!live) continue;
+                const uint32_t sbuf = base + Cfg::ring_bytes + cbuf * TSTAGE_C;
+                if (issuer) tma_wait_read<1>();
+                named_bar_sync(1, 128);
+                const uint32_t rbase = sbuf + row * 128;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t dst = rbase + ((uint32_t)(j ^ (row & 7)) << 4);
+                    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};"
+                                 ::"r"(dst), "r"(v[4 * j]), "r"(v[4 * j + 1]), "r"(v[4 * j + 2]), "r"(v[4 * j + 3]) : "memory");
+                }
+                fence_async_smem();
+                named_bar_sync(1, 128);
+                if (issuer) {
+                    if (reduce) tma_reduce_add_2d(&tm_c, sbuf, n0 + c * TEPI_W, m0);
+                    else        tma_store_2d(&tm_c, sbuf, n0 + c * TEPI_W, m0);
+                    tma_commit();
+                }
+                cbuf ^= 1;
+            }
+        }
+        if (issuer) tma_wait_all();
+    }
+    tc_fence_before();
+    cluster_sync_all();                                     // both CTAs are done with both TMEMs and all barriers
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
 // ---------------------------------------------------------------------------- host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -365,6 +592,8 @@ static thread_local int* t_sched_override = nullptr;
 static thread_local int t_max_tiles = 0;
 static int g_dynamic = 1;            // GAUSS_CUDA_TC_STATIC=1 falls back to static round-robin tiles
 static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
+static int g_pair = 1;               // GAUSS_CUDA_TC_PAIR=0 switches the CTA-pair kernel off
+static thread_local bool t_pair_ok = true;   // callers that need the dynamic tile scheduler (multi-GPU) veto it
 
 bool tc_available()
 {
@@ -386,6 +615,8 @@ int tc_setup_device()
     if (v) g_variant = atoi(v) ? 1 : 0;
     const char* st = getenv("GAUSS_CUDA_TC_STATIC");
     g_dynamic = (st && atoi(st)) ? 0 : 1;
+    const char* pr = getenv("GAUSS_CUDA_TC_PAIR");
+    if (pr) g_pair = atoi(pr) ? 1 : 0;
     const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
     if (rs) g_reserve_sms = atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs));
     int dev = 0;
@@ -398,6 +629,7 @@ int tc_setup_device()
     }
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<32, 2>::smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_gemm_kernel<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<16, 4>::smem_bytes);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_gemm_pair_kernel<32, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg2<32, 3>::smem_bytes);
     return e == cudaSuccess ? GAUSS_CUDA_OK : GAUSS_CUDA_CUDA_ERR;
 }
 
@@ -447,6 +679,29 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     return (int)cudaGetLastError();
 }
 
+// CTA pairs: 256 x 256 tiles, static round-robin over floor(SMs / 2) pairs.  Used for launches with at least two
+// rounds of pair tiles when nothing asks for the dynamic scheduler (bounded CTAs, reserved SMs, multi-GPU callers).
+static int launch_pair(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
+                       float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
+{
+    constexpr int BK = 32, STAGES = 3;
+    using Cfg = TcCfg2<BK, STAGES>;
+    CUtensorMap ta, tal, tb, tbl, tc;
+    int rc = 0;
+    rc |= make_map(&ta, Ahi, k, m, lda, BK, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
+    rc |= make_map(&tal, Alo, k, m, lda, BK, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
+    rc |= make_map(&tb, Bhi, k, n, ldb, BK, TBN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
+    rc |= make_map(&tbl, Blo, k, n, ldb, BK, TBN / 2, CU_TENSOR_MAP_SWIZZLE_128B);
+    rc |= make_map(&tc, C, n, m, ldc, TEPI_W, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return (int)cudaErrorInvalidValue;
+    const int tiles = ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN);
+    const int pairs = std::min(tiles, g_num_sms / 2);
+    tc_gemm_pair_kernel<BK, STAGES><<<2 * pairs, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0);
+    ++g_launch_count;
+    return (int)cudaGetLastError();
+}
+
+void tc_set_pair_ok(bool ok) { t_pair_ok = ok; }
 void tc_set_sched_slots(int* slots) { t_sched_override = slots; }
 void tc_set_max_tiles(int max_tiles) { t_max_tiles = max_tiles; }
 
@@ -455,6 +710,9 @@ int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, co
 {
     if (m <= 0 || n <= 0 || k <= 0) return 0;
     if (!g_encode || (k % 32) != 0) return (int)cudaErrorInvalidValue;
+    if (g_pair && t_pair_ok && t_max_tiles == 0 && g_reserve_sms == 0 && g_variant == 0 &&
+        ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN) >= 2 * (g_num_sms / 2))
+        return launch_pair(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
     if (g_variant == 1) return launch_variant<16, 4>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
     return launch_variant<32, 2>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
 }

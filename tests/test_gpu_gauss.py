@@ -150,6 +150,22 @@ def test_overlapped_upload_is_bit_identical(n, nb, chunks, mode, monkeypatch):
     assert np.array_equal(X1, X2) and np.array_equal(X1, X1b) and np.array_equal(X1, X3) and np.array_equal(B1, B2)
 
 
+def test_cta_pair_kernel_is_bit_identical(monkeypatch):
+    # from ~150 tiles of 256 x 256 the trailing update runs on CTA pairs (tcgen05.mma.cta_group::2); every output
+    # element must see the same MMAs in the same order as in the single-CTA kernel
+    n = 4500                                   # np = 4608: ragged last tile row (18 row blocks of 256), 9 outer blocks
+    A, B, Xtrue = pkg.initialize_inputs(n, 6)
+    with pkg.GaussCuda(n, mode=pkg.MODE_3XTF32) as g:
+        X1 = g.gauss(A, B)
+        LU1 = g.download_factors()
+    monkeypatch.setenv("GAUSS_CUDA_TC_PAIR", "0")
+    with pkg.GaussCuda(n, mode=pkg.MODE_3XTF32) as g:
+        X0 = g.gauss(A, B)
+        LU0 = g.download_factors()
+    assert ol.max_rel_error(X1, Xtrue) <= TOL
+    assert np.array_equal(LU0, LU1) and np.array_equal(X0, X1)
+
+
 @pytest.mark.parametrize("mode", MODES)
 def test_overlapped_upload_reports_singular(mode, monkeypatch):
     monkeypatch.setenv("GAUSS_CUDA_STREAM_MIN_N", "0")
