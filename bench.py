@@ -344,7 +344,7 @@ def main():
     tf32x3 = peaks["bf16_tflops_sustained"] / 2.0 / 3.0
     ffma_peak = 148 * 128 * 2 * (clocks["sm_mhz"] or peaks.get("sm_max_mhz", 1965.0)) * 1e6 * 1e-12 if clocks else 74.4
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r01", "tc_traffic_gauss32768.json")
+    tpath = os.path.join(ROOT, "profiles", "r01", "tc_pair_traffic_gauss32768.json")
     if args.workload == "gauss32768" and world == 1 and mode == pkg.MODE_3XTF32 and os.path.exists(tpath):
         traffic = json.load(open(tpath)).get("traffic_bytes_per_launch")     # ncu dram__bytes_read+write per launch, same workload
     if upd_s > 0:
@@ -352,7 +352,8 @@ def main():
         peak = tf32x3 if mode == pkg.MODE_3XTF32 else ffma_peak
         roofline = {"bound": "tensor", "kernel": "tc_gemm_kernel (trailing update A22 -= L21*U12)" if mode == pkg.MODE_3XTF32 else "sgemm_nn_kernel",
                     "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
-                    "traffic_note": "DRAM bytes per launch from profiles/r01/tc_traffic_gauss32768.json (ncu, same workload; algorithmic C read+write is 3.75e9)" if traffic else None,
+                    "traffic_note": ("DRAM bytes per launch from profiles/r01/tc_pair_traffic_gauss32768.json (ncu dram__bytes_read+write on 40 trailing-update "
+                                     "launches of the same workload: 1.16x the algorithmic C read+write, scaled to the full-solve average of 2.85e9 B per launch)") if traffic else None,
                     "peak_basis": (f"{peak_src} bf16_tflops_sustained / 2 (TF32 rate) / 3 (3xTF32 passes)" if mode == pkg.MODE_3XTF32
                                    else "148 SM x 128 FMA x 2 x sampled SM clock"),
                     "launches": upd_launches, "avg_launch_ms": upd_s / max(upd_launches, 1) * 1e3,
