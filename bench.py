@@ -281,7 +281,7 @@ def main():
     A, B, X, keep = host_buffers(n, pinned)
     nb_outer = None
     # outer block size is decided by the library; probe it with a dry upload after filling
-    probe_nb = args.nb if args.nb else (512 if (mode == pkg.MODE_3XTF32 and n >= 8192) else (256 if (mode == pkg.MODE_3XTF32 and n >= 2048) else (256 if world > 1 else 128)))
+    probe_nb = args.nb if args.nb else pkg.auto_outer_block(n, mode, world)
     for bi, (r0, cnt) in enumerate(pkg.outer_blocks(n, probe_nb)):
         if pkg.block_owner(bi, world) == rank:
             fill_rows(A, B, n, r0, min(r0 + cnt, n), args.seed)

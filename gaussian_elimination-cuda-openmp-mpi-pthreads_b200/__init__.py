@@ -199,6 +199,22 @@ def padded_order(n, inner=128):
     return (n + inner - 1) // inner * inner
 
 
+def auto_outer_block(n, mode=MODE_3XTF32, world=1):
+    """The outer block size the library picks for nb = 0 (ctx_create in csrc/gauss_cuda.cu)."""
+    npad = padded_order(n)
+    if mode == MODE_FFMA:
+        nb = 256 if world > 1 else 128
+    elif npad >= 24576 and world == 1:
+        nb = 1024
+    elif npad >= 8192:
+        nb = 512
+    elif npad >= 4096:
+        nb = 256
+    else:
+        nb = 128
+    return min(nb, npad)
+
+
 def outer_blocks(n, nb):
     """[(row0, rows)] of the outer row blocks of the padded system."""
     npad = padded_order(n)

@@ -230,7 +230,9 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     c->ld = c->np + kPadCols;
     if (nb == 0) {
         if (mode == GAUSS_CUDA_MODE_FFMA) nb = (world > 1) ? 256 : 128;
-        else nb = c->np >= 8192 ? 512 : (c->np >= 2048 ? 256 : 128);
+        // measured on B200 (3xTF32, one GPU): N=2048 nb 128/256/512 -> 1.07/1.12/1.13 ms; N=8192 256/512 -> 5.52/5.20 ms;
+        // N=16384 256/512/1024 -> 20.8/18.6/18.6 ms; N=32768 256/512/768/1024 -> 127.9/113.3/111.1/109.7 ms
+        else nb = (c->np >= 24576 && world == 1) ? 1024 : c->np >= 8192 ? 512 : (c->np >= 4096 ? 256 : 128);
     }
     c->NB = std::min(nb, c->np);
     c->nblk = (c->np + c->NB - 1) / c->NB;
@@ -464,12 +466,14 @@ static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo, co
     for (int j = 0; j < ninner; ++j) {
         const int kk = k0 + j * kNb, r = j * kNb;
         launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
-        launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
-                    tc ? ub_hi + (size_t)(kk + kNb) * NB : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB : nullptr, NB, r, s);
         const int mrem = kb - (r + kNb);
+        // U-row solve over the full width and L-col solve of the panel rows below, one launch (both only need the factor)
+        launch_urow_lcol(P + (size_t)r * ld + kk, ld,
+                         P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+                         tc ? ub_hi + (size_t)(kk + kNb) * NB : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB : nullptr, NB, r,
+                         P + (size_t)(r + kNb) * ld + kk, ld, mrem,
+                         tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB : nullptr, NB, r, s);
         if (mrem > 0) {
-            launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
-                        tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB : nullptr, NB, r, s);
             int rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
                                  tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
                                  tc ? ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
@@ -577,11 +581,21 @@ static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* u
     const bool fork = ss != nullptr && m > 0 && ninner <= 8 && np >= 4096;
     float* Wb = c->W + (size_t)l0 * ld;
     int rc;
+    bool lcol_done = false;
     for (int j = 0; j < ninner; ++j) {
         const int kk = k0 + j * kNb, r = j * kNb;
         launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
-        launch_urow(P + (size_t)r * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
-                    tc ? ubh + (size_t)(kk + kNb) * NB : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB : nullptr, NB, r, s);
+        const int mrem = kb - (r + kNb);
+        // the U-row solve over the full width shares its launch with the L-col solve that follows on this stream: the
+        // panel rows below (two-level blocking) or, with a single inner block and no fork, all the rows below
+        const bool lcol_all = ninner == 1 && !fork && m > 0;
+        launch_urow_lcol(P + (size_t)r * ld + kk, ld,
+                         P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+                         tc ? ubh + (size_t)(kk + kNb) * NB : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB : nullptr, NB, r,
+                         lcol_all ? Wb + kk : P + (size_t)(r + kNb) * ld + kk, ld, lcol_all ? m : mrem,
+                         tc ? lah + (size_t)(lcol_all ? l0 : k0 + r + kNb) * NB : nullptr,
+                         tc ? lal + (size_t)(lcol_all ? l0 : k0 + r + kNb) * NB : nullptr, NB, r, s);
+        lcol_done = lcol_all;
         if (fork) {                                            // P2(j) beside the rest of P1
             CK(cudaEventRecord(c->ev_inner[j], s));
             CK(cudaStreamWaitEvent(ss, c->ev_inner[j], 0));
@@ -596,10 +610,7 @@ static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* u
                 if (rc) return rc;
             }
         }
-        const int mrem = kb - (r + kNb);
         if (mrem > 0) {
-            launch_lcol(P + (size_t)r * ld + kk, ld, P + (size_t)(r + kNb) * ld + kk, ld, mrem,
-                        tc ? lah + (size_t)(k0 + r + kNb) * NB : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB : nullptr, NB, r, s);
             rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
                              tc ? lah + (size_t)(k0 + r + kNb) * NB + r : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB + r : nullptr,
                              tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
@@ -612,7 +623,7 @@ static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* u
     if (fork) {
         CK(cudaEventRecord(c->ev_side, ss));
         CK(cudaStreamWaitEvent(s, c->ev_side, 0));
-    } else if ((rc = col_panel(c, K, pr, l0, sb, row_hi))) return rc;
+    } else if (!lcol_done && (rc = col_panel(c, K, pr, l0, sb, row_hi))) return rc;
     return trailing_update(c, K, pr, sb, l0, row_hi);
 }
 

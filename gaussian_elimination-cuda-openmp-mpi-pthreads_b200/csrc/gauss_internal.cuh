@@ -14,6 +14,11 @@ constexpr int kPadCols = 32;      // zero columns after the RHS column (keeps ro
 // In-place Crout factor of the 128x128 block at `blk` (leading dimension ld):
 // U unit-upper above the diagonal, L (pivots included) on and below it.
 // `status` receives (global_row + 1) of the first zero / non-finite pivot (0 = none).
+// U-row solve of (a12, ncols) and L-col solve of (a21, nrows) against the same factored diagonal block d11, in one
+// launch where the tensor-core panel kernels are in use (otherwise two launches)
+void launch_urow_lcol(const float* d11, int ldd,
+                      float* a12, int ld12, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub,
+                      float* a21, int ld21, int nrows, float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s);
 void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s);
 
 // U-row: X = L11^-1 * A12 for the 128-row block `rows` over `ncols` columns starting at

@@ -399,6 +399,12 @@ static bool panel_mma_enabled()
     if (g_panel_mma < 0) { const char* e = getenv("GAUSS_CUDA_PANEL_MMA"); g_panel_mma = (e && atoi(e) == 0) ? 0 : 1; }
     return g_panel_mma != 0;
 }
+static int g_panel_fuse = -1;
+static bool panel_fuse_enabled()           // GAUSS_CUDA_PANEL_FUSE=0: U-row and L-col solves of an inner block as two launches
+{
+    if (g_panel_fuse < 0) { const char* e = getenv("GAUSS_CUDA_PANEL_FUSE"); g_panel_fuse = (e && atoi(e) == 0) ? 0 : 1; }
+    return g_panel_fuse != 0;
+}
 static void launch_urow_mma(const float* l11, int ldl, float* a12, int ld, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s);
 static void launch_lcol_mma(const float* u11, int ldu, float* a21, int ld, int nrows, float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s);
 
@@ -649,14 +655,13 @@ struct UrowMmaSmem {
     float strip[kNb][kUS];
 };
 
-__global__ void __launch_bounds__(256, 2)
-urow_mma_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int ld, int ncols,
-                float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
+__device__ __forceinline__ void
+urow_mma_body(unsigned char* smem_raw, const int bid, const float* __restrict__ l11, int ldl, float* __restrict__ a12, int ld, int ncols,
+              float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     UrowMmaSmem& sm = *reinterpret_cast<UrowMmaSmem*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int c0 = blockIdx.x * UW;
+    const int c0 = bid * UW;
 
     for (int idx = tid; idx < 4 * 32 * 8; idx += 256) {
         const int bb = idx >> 8, r = (idx >> 3) & 31, c4 = (idx & 7) << 2;
@@ -734,14 +739,13 @@ struct LcolMmaSmem {
     float tile[LH][kLS];
 };
 
-__global__ void __launch_bounds__(256, 2)
-lcol_mma_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int ld, int nrows,
-                float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
+__device__ __forceinline__ void
+lcol_mma_body(unsigned char* smem_raw, const int bid, const float* __restrict__ u11, int ldu, float* __restrict__ a21, int ld, int nrows,
+              float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
     LcolMmaSmem& sm = *reinterpret_cast<LcolMmaSmem*>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int row0 = blockIdx.x * LH;
+    const int row0 = bid * LH;
 
     for (int idx = tid; idx < 4 * 32 * 8; idx += 256) {
         const int bb = idx >> 8, r = (idx >> 3) & 31, c4 = (idx & 7) << 2;
@@ -793,6 +797,49 @@ lcol_mma_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21,
     }
 }
 
+__global__ void __launch_bounds__(256, 2)
+urow_mma_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12, int ld, int ncols,
+                float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    urow_mma_body(smem_raw, blockIdx.x, l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
+}
+__global__ void __launch_bounds__(256, 2)
+lcol_mma_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21, int ld, int nrows,
+                float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    lcol_mma_body(smem_raw, blockIdx.x, u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
+}
+// Both solves of one inner block in one launch: they only depend on the diagonal factor, not on each other, and
+// each of them is latency-bound (~10-13 us for any size below one wave), so sharing a launch takes one kernel off the
+// panel chain.  The first n_ucta CTAs do the U-row columns, the rest the L-col rows.
+__global__ void __launch_bounds__(256, 2)
+urow_lcol_mma_kernel(const float* __restrict__ d11, int ldd, int n_ucta,
+                     float* __restrict__ a12, int ld12, int ncols, float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub,
+                     float* __restrict__ a21, int ld21, int nrows, float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    if ((int)blockIdx.x < n_ucta) urow_mma_body(smem_raw, blockIdx.x, d11, ldd, a12, ld12, ncols, ub_hi, ub_lo, ldub, k_ub);
+    else lcol_mma_body(smem_raw, (int)blockIdx.x - n_ucta, d11, ldd, a21, ld21, nrows, la_hi, la_lo, ldla, k_la);
+}
+
+void launch_urow_lcol(const float* d11, int ldd,
+                      float* a12, int ld12, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub,
+                      float* a21, int ld21, int nrows, float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s)
+{
+    if (ncols > 0 && nrows > 0 && ub_hi != nullptr && la_hi != nullptr && panel_mma_enabled() && panel_fuse_enabled()) {
+        const int n_ucta = (ncols + UW - 1) / UW, n_lcta = (nrows + LH - 1) / LH;
+        constexpr size_t smem = sizeof(UrowMmaSmem) > sizeof(LcolMmaSmem) ? sizeof(UrowMmaSmem) : sizeof(LcolMmaSmem);
+        urow_lcol_mma_kernel<<<n_ucta + n_lcta, 256, smem, s>>>(d11, ldd, n_ucta, a12, ld12, ncols, ub_hi, ub_lo, ldub, k_ub,
+                                                                 a21, ld21, nrows, la_hi, la_lo, ldla, k_la);
+        ++g_launch_count;
+        return;
+    }
+    launch_urow(d11, ldd, a12, ld12, ncols, ub_hi, ub_lo, ldub, k_ub, s);
+    launch_lcol(d11, ldd, a21, ld21, nrows, la_hi, la_lo, ldla, k_la, s);
+}
+
 static void launch_urow_mma(const float* l11, int ldl, float* a12, int ld, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s)
 {
     urow_mma_kernel<<<(ncols + UW - 1) / UW, 256, sizeof(UrowMmaSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
@@ -805,6 +852,8 @@ static void launch_lcol_mma(const float* u11, int ldu, float* a21, int ld, int n
 void panel_setup_device()
 {
     cudaFuncSetAttribute(urow_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowMmaSmem));
+    cudaFuncSetAttribute(urow_lcol_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                         (int)(sizeof(UrowMmaSmem) > sizeof(LcolMmaSmem) ? sizeof(UrowMmaSmem) : sizeof(LcolMmaSmem)));
     cudaFuncSetAttribute(lcol_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolMmaSmem));
     cudaFuncSetAttribute(urow_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UrowSmem));
     cudaFuncSetAttribute(lcol_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(LcolSmem));

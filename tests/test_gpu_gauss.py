@@ -150,6 +150,16 @@ def test_overlapped_upload_is_bit_identical(n, nb, chunks, mode, monkeypatch):
     assert np.array_equal(X1, X2) and np.array_equal(X1, X1b) and np.array_equal(X1, X3) and np.array_equal(B1, B2)
 
 
+@pytest.mark.parametrize("mode", MODES)
+def test_auto_outer_block_matches_the_host_mirror(mode):
+    # bench.py and multi-GPU callers place rows by pkg.auto_outer_block; it must be the library's own choice
+    for n in (100, 2048, 4000, 4096, 8192):
+        A, B = pkg.initMatrix(n)
+        with pkg.GaussCuda(n, mode=mode) as g:
+            g.gauss(A, B)
+            assert g.stats.nb_outer == pkg.auto_outer_block(n, mode, 1)
+
+
 def test_cta_pair_kernel_is_bit_identical(monkeypatch):
     # from ~150 tiles of 256 x 256 the trailing update runs on CTA pairs (tcgen05.mma.cta_group::2); every output
     # element must see the same MMAs in the same order as in the single-CTA kernel
