@@ -138,6 +138,7 @@ struct gauss_cuda_ctx {
     cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
     bool overlap = false;
     int overlap_max_tiles = 3;
+    bool dist_pair = true;                      // GAUSS_CUDA_DIST_PAIR=0: multi-GPU updates stay on the single-CTA kernel
     float* ub_hi[2] = {nullptr, nullptr};       // [ld x NB]          split U operand, transposed;
     float* ub_lo[2] = {nullptr, nullptr};       //                    second copy only when world > 1 (look-ahead)
     float* xvec = nullptr;   // [np] solution
@@ -223,6 +224,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         const char* mt = getenv("GAUSS_CUDA_OVERLAP_TILES");
         if (mt && atoi(mt) > 0) c->overlap_max_tiles = atoi(mt);
     }
+    { const char* e = getenv("GAUSS_CUDA_DIST_PAIR"); if (e && atoi(e) == 0) c->dist_pair = false; }
     { const char* e = getenv("GAUSS_CUDA_STREAM"); if (e && atoi(e) == 0) c->stream_on = false; }
     { const char* e = getenv("GAUSS_CUDA_STREAM_MIN_N"); if (e) c->stream_min_n = atoi(e); }
     { const char* e = getenv("GAUSS_CUDA_STREAM_CHUNKS"); if (e && atoi(e) > 0) c->stream_chunks = atoi(e); }
@@ -429,7 +431,7 @@ static int gemm_update(gauss_cuda_ctx* c, cudaStream_t s, const float* A, int ld
     }
     tc_set_sched_slots(c->sched);
     tc_set_max_tiles(max_tiles);
-    tc_set_pair_ok(c->world == 1);             // multi-GPU steps share SMs with NCCL: they need the dynamic scheduler
+    tc_set_pair_ok(c->world == 1 || c->dist_pair);
     int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, s);
     tc_set_max_tiles(0);
     tc_set_sched_slots(nullptr);

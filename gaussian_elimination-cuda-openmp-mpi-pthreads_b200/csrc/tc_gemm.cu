@@ -358,7 +358,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
 //   empty[s]   (both)           tcgen05.commit ... multicast to both CTAs
 //   tfull[a]   (both)           tcgen05.commit ... multicast: accumulator `a` complete
 //   tempty[a]  (even CTA only)  256 arrivals: the 128 epilogue threads of each CTA (the odd CTA's arrive remotely)
-// Tiles are assigned round-robin to the pairs (both CTAs derive the same sequence; no queue).  Each output element
+// Tiles come from the same dynamic scheduler as in the single-CTA kernel; the even CTA's producer draws the tile
+// and publishes it into both CTAs' queues (remote store + cluster-scope mbarrier arrive).  Each output element
 // sees the same MMAs in the same order as in the single-CTA kernel, so results are bit-identical.
 constexpr int TBM2 = 256;
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;            // shared::cluster address -> the even CTA of the pair
@@ -395,6 +396,41 @@ __device__ __forceinline__ void mbar_arrive_even(uint32_t bar)        // arrive 
 {
     asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(bar & kPeerBitMask) : "memory");
 }
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t addr, uint32_t rank)     // same smem offset in CTA `rank` of the cluster
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_u32(uint32_t cluster_addr, int v)
+{
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(cluster_addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr)     // release at cluster scope: orders the remote store above
+{
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cl(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait_cl(uint32_t bar, uint32_t parity)    // bounded, acquire at cluster scope
+{
+    if (mbar_try_wait_cl(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait_cl(bar, parity)) {
+        if (clock64() - t0 > 4000000000LL) {
+            printf("tc_gemm_pair: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+            __trap();
+        }
+    }
+}
 __device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate)
 {
     asm volatile(
@@ -426,7 +462,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTcThreads, 1)
 tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant__ CUtensorMap tm_alo,
                     const __grid_constant__ CUtensorMap tm_bhi, const __grid_constant__ CUtensorMap tm_blo,
                     const __grid_constant__ CUtensorMap tm_c,
-                    int m, int n, int k, int negate, int reduce)
+                    int m, int n, int k, int negate, int reduce, int* __restrict__ sched, int dynamic, int max_tiles)
 {
     using Cfg = TcCfg2<BK, STAGES>;
     extern __shared__ unsigned char smem_dyn[];
@@ -437,7 +473,13 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
     auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    // tile queue (as in the single-CTA kernel), one copy per CTA: the even CTA's producer draws the tile and
+    // publishes it to both; qempty lives in the even CTA and collects every consumer of both CTAs
+    auto qfull_bar = [&](int q) { return bar_base + 8u * (2 * STAGES + 5 + q); };
+    auto qempty_bar = [&](int q) { return bar_base + 8u * (2 * STAGES + 9 + q); };
+    const uint32_t q_tile_u32 = bar_base + 8u * (2 * STAGES + 13);
     unsigned char* gen_base = smem_dyn + (base - smem_u32(smem_dyn));
+    volatile int* q_tile = reinterpret_cast<volatile int*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 13));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();                // 0: even CTA (issues the MMAs), 1: its peer
@@ -450,6 +492,8 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 256); }
+        // consumers of a queue slot: even CTA = MMA issuer + 128 epilogue threads, odd CTA = producer + 128 epilogue threads
+        for (int q = 0; q < 4; ++q) { mbar_init(qfull_bar(q), 1); mbar_init(qempty_bar(q), 2 * (1 + 128)); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {                                        // both CTAs, same warp: the pair allocates together
@@ -465,7 +509,28 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
         // ===================== TMA producer (both CTAs) =====================
         if (elect_one()) {
             int stage = 0; uint32_t phase = 0;
-            for (int t = pair; t < num_tiles; t += num_pairs) {
+            for (int it = 0;; ++it) {
+                const int q = it & 3;
+                int t;
+                if (rank == 0) {
+                    // same policy as the single-CTA kernel: dynamic == 1 first tile static, the rest from the counter;
+                    // dynamic == 2 (bounded CTAs) every tile from the counter; 0 static round-robin over the pairs
+                    if (max_tiles > 0 && it >= max_tiles) t = -1;
+                    else if (dynamic == 2) t = atomicAdd(sched, 1);
+                    else if (it == 0 || !dynamic) t = pair + it * num_pairs;
+                    else t = atomicAdd(sched, 1) + num_pairs;
+                    if (t >= num_tiles) t = -1;
+                    mbar_wait_cl(qempty_bar(q), ((it >> 2) & 1) ^ 1);
+                    q_tile[q] = t;
+                    st_cluster_u32(mapa_u32(q_tile_u32 + 4u * q, 1), t);
+                    mbar_arrive(qfull_bar(q));
+                    mbar_arrive_cluster(mapa_u32(qfull_bar(q), 1));
+                } else {
+                    mbar_wait_cl(qfull_bar(q), (it >> 2) & 1);
+                    t = q_tile[q];
+                    mbar_arrive_cluster(mapa_u32(qempty_bar(q), 0));
+                }
+                if (t < 0) break;
                 int m0, n0;
                 tile_coords2(t, num_m, num_n, m0, n0);
                 const int am = m0 + (int)rank * TBM, bn = n0 + (int)rank * (TBN / 2);
@@ -488,8 +553,12 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((negate ? 1u : 0u) << 13) |
                                    ((uint32_t)(TBN >> 3) << 17) | ((uint32_t)(TBM2 >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
-            int it = 0;
-            for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+            for (int it = 0;; ++it) {
+                const int q = it & 3;
+                mbar_wait_cl(qfull_bar(q), (it >> 2) & 1);
+                const int t = q_tile[q];
+                mbar_arrive_cluster(mapa_u32(qempty_bar(q), 0));
+                if (t < 0) break;
                 const int as = it & 1;
                 const uint32_t aphase = (it >> 1) & 1;
                 mbar_wait(tempty_bar(as), aphase ^ 1);
@@ -522,8 +591,13 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
         const int row = q * 32 + lane;
         const bool issuer = (threadIdx.x == 64);
         int cbuf = 0;
-        int it = 0;
-        for (int t = pair; t < num_tiles; t += num_pairs, ++it) {
+        const uint32_t qe0 = mapa_u32(qempty_bar(0), 0);
+        for (int it = 0;; ++it) {
+            const int qs = it & 3;
+            mbar_wait_cl(qfull_bar(qs), (it >> 2) & 1);
+            const int t = q_tile[qs];
+            mbar_arrive_cluster(qe0 + 8u * qs);
+            if (t < 0) break;
             int m0, n0;
             tile_coords2(t, num_m, num_n, m0, n0);
             m0 += (int)rank * TBM;
@@ -569,6 +643,11 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+    // the last CTA to leave rearms the scheduler slot for a later launch (sched[0] tile counter, sched[1] exits)
+    if (dynamic && threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(sched + 1, 1) == (int)gridDim.x - 1) { sched[0] = 0; sched[1] = 0; __threadfence(); }
     }
 }
 
@@ -679,8 +758,8 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     return (int)cudaGetLastError();
 }
 
-// CTA pairs: 256 x 256 tiles, static round-robin over floor(SMs / 2) pairs.  Used for launches with at least two
-// rounds of pair tiles when nothing asks for the dynamic scheduler (bounded CTAs, reserved SMs, multi-GPU callers).
+// CTA pairs: 256 x 256 tiles over floor(SMs / 2) pairs, same scheduling policy as launch_variant.  Used for launches
+// with at least two rounds of pair tiles.
 static int launch_pair(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
                        float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
 {
@@ -695,8 +774,21 @@ static int launch_pair(const float* Ahi, const float* Alo, int lda, const float*
     rc |= make_map(&tc, C, n, m, ldc, TEPI_W, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return (int)cudaErrorInvalidValue;
     const int tiles = ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN);
-    const int pairs = std::min(tiles, g_num_sms / 2);
-    tc_gemm_pair_kernel<BK, STAGES><<<2 * pairs, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0);
+    const int avail = (g_num_sms - g_reserve_sms) / 2;
+    int pairs = std::min(tiles, avail);
+    int dyn = (g_dynamic && tiles > pairs) ? 1 : 0;
+    int max_tiles = 0;
+    if (t_max_tiles > 0 && g_dynamic && tiles > avail * t_max_tiles / 2) {     // bounded CTAs, as in launch_variant
+        max_tiles = t_max_tiles;
+        pairs = (tiles + max_tiles - 1) / max_tiles;
+        dyn = 2;
+    }
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
+    int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
+    tc_gemm_pair_kernel<BK, STAGES><<<2 * pairs, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0,
+                                                                                   sched, dyn, max_tiles);
     ++g_launch_count;
     return (int)cudaGetLastError();
 }
@@ -710,7 +802,7 @@ int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, co
 {
     if (m <= 0 || n <= 0 || k <= 0) return 0;
     if (!g_encode || (k % 32) != 0) return (int)cudaErrorInvalidValue;
-    if (g_pair && t_pair_ok && t_max_tiles == 0 && g_reserve_sms == 0 && g_variant == 0 &&
+    if (g_pair && t_pair_ok && g_variant == 0 &&
         ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN) >= 2 * (g_num_sms / 2))
         return launch_pair(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
     if (g_variant == 1) return launch_variant<16, 4>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
