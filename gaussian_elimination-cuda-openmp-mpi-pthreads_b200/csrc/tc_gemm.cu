@@ -695,7 +695,7 @@ int tc_setup_device()
     const char* st = getenv("GAUSS_CUDA_TC_STATIC");
     g_dynamic = (st && atoi(st)) ? 0 : 1;
     const char* pr = getenv("GAUSS_CUDA_TC_PAIR");
-    if (pr) g_pair = atoi(pr) ? 1 : 0;
+    g_pair = pr ? (atoi(pr) ? 1 : 0) : 1;
     const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
     if (rs) g_reserve_sms = atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs));
     int dev = 0;

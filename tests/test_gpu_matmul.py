@@ -42,6 +42,24 @@ def test_seeded_uniform(mode):
     assert np.max(np.abs(Cg - C64) / bound) <= TOL
 
 
+def test_large_matmul_runs_on_cta_pairs_and_matches(monkeypatch):
+    # from ~150 tiles of 256 x 256 the multiply runs on CTA pairs (plain TMA store epilogue, ragged last tiles);
+    # it must agree with float64 within the componentwise bound and bit for bit with the single-CTA kernel
+    n = 4100
+    rng = np.random.default_rng(5)
+    A = rng.uniform(-1, 1, (n, n)).astype(np.float32)
+    B = rng.uniform(-1, 1, (n, n)).astype(np.float32)
+    C1, _ = pkg.matmul_cuda(A, B, mode=pkg.MODE_3XTF32)
+    monkeypatch.setenv("GAUSS_CUDA_TC_PAIR", "0")
+    C0, _ = pkg.matmul_cuda(A, B, mode=pkg.MODE_3XTF32)
+    monkeypatch.delenv("GAUSS_CUDA_TC_PAIR")
+    pkg.matmul_cuda(np.eye(32, dtype=np.float32), np.eye(32, dtype=np.float32), mode=pkg.MODE_3XTF32)   # re-read the switch
+    C64 = A.astype(np.float64) @ B.astype(np.float64)
+    bound = np.abs(A).astype(np.float64) @ np.abs(B).astype(np.float64)
+    assert np.max(np.abs(C1 - C64) / bound) <= TOL
+    assert np.array_equal(C0, C1)
+
+
 @pytest.mark.parametrize("variant", ["0", "1"])
 def test_tile_engine_variants(variant):
     # both shared-memory pipelines of the tcgen05 kernel (128 B swizzle x 2 stages, 64 B swizzle x 4 stages)
