@@ -134,6 +134,9 @@ struct gauss_cuda_ctx {
     float* la_lo[2] = {nullptr, nullptr};       //                    second copy for the single-GPU look-ahead
     cudaStream_t s_panel = nullptr;             // higher-priority stream of the single-GPU look-ahead
     cudaStream_t s_side = nullptr;              // side stream of the single-GPU schedule: P2(j) beside the rest of P1
+    cudaStream_t s_wide = nullptr;              // single GPU: the part of P1 right of the panel, beside its in-panel chain
+    cudaEvent_t ev_wide = nullptr;
+    bool wide_split = true;                     // GAUSS_CUDA_WIDE_SPLIT=0 keeps P1 on one stream
     cudaEvent_t ev_inner[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, ev_side = nullptr;
     cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
     bool overlap = false;
@@ -225,6 +228,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         if (mt && atoi(mt) > 0) c->overlap_max_tiles = atoi(mt);
     }
     { const char* e = getenv("GAUSS_CUDA_DIST_PAIR"); if (e && atoi(e) == 0) c->dist_pair = false; }
+    { const char* e = getenv("GAUSS_CUDA_WIDE_SPLIT"); if (e && atoi(e) == 0) c->wide_split = false; }
     { const char* e = getenv("GAUSS_CUDA_STREAM"); if (e && atoi(e) == 0) c->stream_on = false; }
     { const char* e = getenv("GAUSS_CUDA_STREAM_MIN_N"); if (e) c->stream_min_n = atoi(e); }
     { const char* e = getenv("GAUSS_CUDA_STREAM_CHUNKS"); if (e && atoi(e) > 0) c->stream_chunks = atoi(e); }
@@ -270,6 +274,10 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     const bool dist_fork = world > 1 && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0);
     if ((world == 1 && !(getenv("GAUSS_CUDA_INNER_FORK") && atoi(getenv("GAUSS_CUDA_INNER_FORK")) == 0)) || dist_fork) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_side, cudaStreamNonBlocking);
+        if (world == 1 && c->wide_split) {
+            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_wide, cudaStreamNonBlocking);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_wide, cudaEventDisableTiming);
+        }
         for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_inner[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_side, cudaEventDisableTiming);
     }
@@ -343,6 +351,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     if (c->s_comm) cudaStreamSynchronize(c->s_comm);
     if (c->s_panel) cudaStreamSynchronize(c->s_panel);
     if (c->s_side) cudaStreamSynchronize(c->s_side);
+    if (c->s_wide) cudaStreamSynchronize(c->s_wide);
     float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi[0], c->la_lo[0], c->la_hi[1], c->la_lo[1],
                      c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
@@ -381,6 +390,8 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     for (auto& ev : c->ev_inner) if (ev) cudaEventDestroy(ev);
     if (c->ev_side) cudaEventDestroy(c->ev_side);
     if (c->s_side) cudaStreamDestroy(c->s_side);
+    if (c->ev_wide) cudaEventDestroy(c->ev_wide);
+    if (c->s_wide) cudaStreamDestroy(c->s_wide);
     if (c->s_main) cudaStreamDestroy(c->s_main);
     delete c;
 }
@@ -571,7 +582,7 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const S
 // L-col, panel update -- leaves most of the GPU idle); both streams join before P3.
 static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* ubl)
 {
-    cudaStream_t s = c->s_main, ss = c->s_side;
+    cudaStream_t s = c->s_main, ss = c->s_side, sw = c->s_wide;
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     float* lah = c->la_hi[0]; float* lal = c->la_lo[0];
@@ -581,47 +592,72 @@ static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* u
     const int l0 = k0 + kb, m = row_hi - l0;                   // rows below the panel (of those present)
     // (below ~4096 the two-branch CUDA graph costs more launch latency, ~0.2 ms, than the fork saves)
     const bool fork = ss != nullptr && m > 0 && ninner <= 8 && np >= 4096;
+    // P1 split at the right edge of the panel: the next diagonal factor only needs the in-panel part of the U-row
+    // solve and of the rank-128 update (a few CTAs each), so that chain stays on the main stream; the part right of
+    // the panel -- up to two waves of U-row CTAs and a full-width update per inner block at N = 32768 -- follows
+    // on its own stream, one inner block behind
+    const bool split = sw != nullptr && ninner >= 2 && ninner <= 8 && np >= 8192;
+    const int csplit = k0 + kb;                                // first column right of the panel
     float* Wb = c->W + (size_t)l0 * ld;
     int rc;
     bool lcol_done = false;
     for (int j = 0; j < ninner; ++j) {
         const int kk = k0 + j * kNb, r = j * kNb;
-        launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
+        float* D = P + (size_t)r * ld + kk;                    // diagonal block of inner block j
+        launch_diag_factor(D, ld, kk, c->status, s);
         const int mrem = kb - (r + kNb);
-        // the U-row solve over the full width shares its launch with the L-col solve that follows on this stream: the
-        // panel rows below (two-level blocking) or, with a single inner block and no fork, all the rows below
+        // the U-row solve shares its launch with the L-col solve that follows on this stream: the panel rows below
+        // (two-level blocking) or, with a single inner block and no fork, all the rows below
         const bool lcol_all = ninner == 1 && !fork && m > 0;
-        launch_urow_lcol(P + (size_t)r * ld + kk, ld,
-                         P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+        const int ucols = split ? csplit - (kk + kNb) : np + 1 - (kk + kNb);
+        launch_urow_lcol(D, ld,
+                         D + kNb, ld, ucols,
                          tc ? ubh + (size_t)(kk + kNb) * NB : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB : nullptr, NB, r,
                          lcol_all ? Wb + kk : P + (size_t)(r + kNb) * ld + kk, ld, lcol_all ? m : mrem,
                          tc ? lah + (size_t)(lcol_all ? l0 : k0 + r + kNb) * NB : nullptr,
                          tc ? lal + (size_t)(lcol_all ? l0 : k0 + r + kNb) * NB : nullptr, NB, r, s);
         lcol_done = lcol_all;
+        if (fork || split) CK(cudaEventRecord(c->ev_inner[j], s));
+        if (split) {                                           // right of the panel: U-row solve, then the update of the panel rows below
+            CK(cudaStreamWaitEvent(sw, c->ev_inner[j], 0));
+            launch_urow(D, ld, P + (size_t)r * ld + csplit, ld, np + 1 - csplit,
+                        tc ? ubh + (size_t)csplit * NB : nullptr, tc ? ubl + (size_t)csplit * NB : nullptr, NB, r, sw);
+            if (mrem > 0) {
+                rc = gemm_update(c, sw, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + csplit, ld,
+                                 tc ? lah + (size_t)(k0 + r + kNb) * NB + r : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB + r : nullptr,
+                                 tc ? ubh + (size_t)csplit * NB + r : nullptr, tc ? ubl + (size_t)csplit * NB + r : nullptr,
+                                 P + (size_t)(r + kNb) * ld + csplit, mrem, ld - csplit, kNb);
+                if (rc) return rc;
+            }
+        }
         if (fork) {                                            // P2(j) beside the rest of P1
-            CK(cudaEventRecord(c->ev_inner[j], s));
             CK(cudaStreamWaitEvent(ss, c->ev_inner[j], 0));
-            launch_lcol(P + (size_t)r * ld + kk, ld, Wb + kk, ld, m,
+            launch_lcol(D, ld, Wb + kk, ld, m,
                         tc ? lah + (size_t)l0 * NB : nullptr, tc ? lal + (size_t)l0 * NB : nullptr, NB, r, ss);
             const int nin = kb - (r + kNb);
             if (nin > 0) {
-                rc = gemm_update(c, ss, Wb + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+                rc = gemm_update(c, ss, Wb + kk, ld, D + kNb, ld,
                                  tc ? lah + (size_t)l0 * NB + r : nullptr, tc ? lal + (size_t)l0 * NB + r : nullptr,
                                  tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
                                  Wb + kk + kNb, m, nin, kNb);
                 if (rc) return rc;
             }
         }
-        if (mrem > 0) {
-            rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+        if (mrem > 0) {                                        // rank-128 update of the panel rows below (in-panel columns only when split)
+            const int gcols = split ? csplit - (kk + kNb) : ld - (kk + kNb);
+            rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, D + kNb, ld,
                              tc ? lah + (size_t)(k0 + r + kNb) * NB + r : nullptr, tc ? lal + (size_t)(k0 + r + kNb) * NB + r : nullptr,
                              tc ? ubh + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ubl + (size_t)(kk + kNb) * NB + r : nullptr,
-                             P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
+                             P + (size_t)(r + kNb) * ld + kk + kNb, mrem, gcols, kNb);
             if (rc) return rc;
         }
     }
     const float* P0 = P + k0;
     PanelRef pr{P0, ld, P0 + kb, ld, ubh, ubl};
+    if (split) {
+        CK(cudaEventRecord(c->ev_wide, sw));
+        CK(cudaStreamWaitEvent(s, c->ev_wide, 0));
+    }
     if (fork) {
         CK(cudaEventRecord(c->ev_side, ss));
         CK(cudaStreamWaitEvent(s, c->ev_side, 0));

@@ -160,6 +160,24 @@ def test_auto_outer_block_matches_the_host_mirror(mode):
             assert g.stats.nb_outer == pkg.auto_outer_block(n, mode, 1)
 
 
+def test_wide_split_of_the_row_panel_is_bit_identical(monkeypatch):
+    # from n = 8192 the part of the row-panel factorisation right of the panel runs on its own stream, one inner block
+    # behind the in-panel chain; same kernels and arithmetic, different launch ranges and order
+    n = 8200                                   # np = 8320: 16 full outer blocks of 512 and a ragged one of 128
+    A, B, Xtrue = pkg.initialize_inputs(n, 2)
+    Xtrue = None
+    with pkg.GaussCuda(n, mode=pkg.MODE_3XTF32) as g:
+        X1 = g.gauss(A, B)
+        g.upload(A, B)
+        g.solve_resident()                     # graph replay of the same schedule
+        X1r = g.download()
+    monkeypatch.setenv("GAUSS_CUDA_WIDE_SPLIT", "0")
+    with pkg.GaussCuda(n, mode=pkg.MODE_3XTF32) as g:
+        X0 = g.gauss(A, B)
+    assert ol.scaled_residual(A, B, X1) <= 10.0
+    assert np.array_equal(X0, X1) and np.array_equal(X1, X1r)
+
+
 def test_cta_pair_kernel_is_bit_identical(monkeypatch):
     # from ~150 tiles of 256 x 256 the trailing update runs on CTA pairs (tcgen05.mma.cta_group::2); every output
     # element must see the same MMAs in the same order as in the single-CTA kernel
