@@ -364,6 +364,9 @@ def main():
             # exceeds it, so the fraction against the burst-derived ceiling is reported beside it
             roofline["peak_burst"] = peaks["bf16_tflops"] / 6.0
             roofline["frac_of_burst"] = ach / roofline["peak_burst"]
+            # every credited flop is three TF32 MMAs: the dense TF32 rate this kernel sustains is the direct probe of the
+            # tensor pipe SURVEY 8(d) asks for (cuBLAS bf16 / 2 underestimates it)
+            roofline["tf32_mma_tflops_sustained_by_kernel"] = 3.0 * ach
             roofline["kernel"] = "tc_gemm_pair_kernel / tc_gemm_kernel (trailing update A22 -= L21*U12)"
     else:
         roofline = None

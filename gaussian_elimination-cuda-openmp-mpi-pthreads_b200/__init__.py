@@ -26,7 +26,7 @@ OK, ZERO_PIVOT, BAD_ARG, CUDA_ERR, NCCL_ERR, NOT_READY = range(6)
 # every symbol include/gauss_cuda.h declares (tests check the library exports them all)
 ABI_SYMBOLS = (
     "gauss_cuda_init", "gauss_cuda_unique_id", "gauss_cuda_init_dist", "gauss_cuda_solve",
-    "gauss_cuda_upload", "gauss_cuda_solve_resident", "gauss_cuda_download",
+    "gauss_cuda_upload", "gauss_cuda_init_matrix_device", "gauss_cuda_solve_resident", "gauss_cuda_download",
     "gauss_cuda_compute_gauss", "gauss_cuda_solve_gauss", "gauss_cuda_download_factors",
     "gauss_cuda_set_pivoting", "gauss_cuda_get_pivots", "gauss_cuda_solve_refined", "gauss_cuda_free", "matmul_cuda", "matmul_cuda_device", "matmul_cuda_device_noalloc",
     "gauss_host_init_matrix", "gauss_host_initialize_inputs", "gauss_host_matmul_fill",
@@ -93,6 +93,7 @@ def lib():
         L.gauss_cuda_init_dist.argtypes = [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int]
         L.gauss_cuda_solve.argtypes = [vp, _fp, _fp, _fp, _fp, C.POINTER(GaussStats)]
         L.gauss_cuda_upload.argtypes = [vp, _fp, _fp]
+        L.gauss_cuda_init_matrix_device.argtypes = [vp]
         L.gauss_cuda_solve_resident.argtypes = [vp, C.POINTER(GaussStats)]
         L.gauss_cuda_compute_gauss.argtypes = [vp, C.POINTER(GaussStats)]
         L.gauss_cuda_solve_gauss.argtypes = [vp, C.POINTER(GaussStats)]
@@ -277,6 +278,10 @@ class GaussCuda:
     def upload(self, A, B):
         A32, B32 = _f32(A), _f32(B)
         _check(lib().gauss_cuda_upload(self._h, A32.ctypes.data_as(_fp), B32.ctypes.data_as(_fp)))
+
+    def initMatrix_device(self):
+        """initMatrix (gauss_internal_input.c:50-60) generated on the GPU into the resident copy (no host data, no upload)."""
+        _check(lib().gauss_cuda_init_matrix_device(self._h))
 
     def upload_ptr(self, a_ptr, b_ptr):
         """Same, from raw host addresses (e.g. pinned torch tensors): no copies made here."""

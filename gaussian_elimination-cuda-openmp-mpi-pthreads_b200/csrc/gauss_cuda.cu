@@ -1175,6 +1175,29 @@ extern "C" int gauss_cuda_upload(gauss_cuda_ctx* c, const float* A, const float*
     return GAUSS_CUDA_OK;
 }
 
+// initMatrix (gauss_internal_input.c:50-60) generated on the device, straight into the resident copy: the fixture
+// never exists on the host and "Application time" loses the 4 N^2-byte upload.  Works for every rank of a group.
+extern "C" int gauss_cuda_init_matrix_device(gauss_cuda_ctx* c)
+{
+    if (!c) return GAUSS_CUDA_BAD_ARG;
+    CK(cudaSetDevice(c->device));
+    if (!c->W0) CK(cudaMalloc((void**)&c->W0, (size_t)std::max(c->rows_local, 1) * c->ld * sizeof(float)));
+    cudaStream_t s = c->s_main;
+    const int n = c->n;
+    for (int R = c->rank; R < c->nblk; R += c->world) {
+        const int g0 = R * c->NB, l0 = blk_local_row(c, R), rows = blk_rows(c, R);
+        const int real = std::max(0, std::min(rows, n - g0));
+        launch_init_fixture(c->W0, c->ld, l0, g0, real, n, c->np, s);
+        if (real > 0) launch_pad_identity(c->W0, c->ld, l0, g0, real, n, n, s);
+        if (rows > real) launch_pad_identity(c->W0, c->ld, l0 + real, g0 + real, rows - real, n, 0, s);
+    }
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(s));
+    c->resident = true;
+    c->factored = false;
+    return GAUSS_CUDA_OK;
+}
+
 static int restore_working(gauss_cuda_ctx* c)
 {
     CK(cudaMemcpyAsync(c->W, c->W0, (size_t)c->rows_local * c->ld * sizeof(float), cudaMemcpyDeviceToDevice, c->s_main));

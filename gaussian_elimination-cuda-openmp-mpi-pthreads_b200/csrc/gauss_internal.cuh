@@ -53,6 +53,7 @@ void launch_residual_f64(const double* A, const double* x, const double* b, doub
 void launch_refine_update(double* x, const float* d, int n, double* out, cudaStream_t s);
 
 // Layout helpers: scatter the dense RHS into column `col` / gather it back; identity padding.
+void launch_init_fixture(float* w, int ld, int row0_local, int g0, int nrows, int n, int ycol, cudaStream_t s);
 void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s);
 void launch_get_column(const float* w, int ld, int col, float* dst, int nrows, cudaStream_t s);
 void launch_pad_identity(float* w, int ld, int row0_local, int row0_global, int nrows, int n, int col0, cudaStream_t s);

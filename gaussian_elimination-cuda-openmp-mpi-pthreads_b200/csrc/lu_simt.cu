@@ -437,6 +437,26 @@ __global__ void pad_identity_kernel(float* w, int ld, int row0_local, int row0_g
     w[(size_t)(row0_local + r) * ld + c] = (g >= n && c == g) ? 1.f : 0.f;
 }
 
+// initMatrix on the device (gauss_internal_input.c:50-60): matrix[i][j] = 2 (min(i, j) + 1), B[i] = i, for `nrows`
+// local rows starting at global row g0; the RHS lives in column ycol.  Rows / columns beyond n are left to pad_identity.
+__global__ void init_fixture_kernel(float* __restrict__ w, int ld, int row0_local, int g0, int nrows, int n, int ycol)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y;
+    const int i = g0 + r;
+    if (r >= nrows || i >= n) return;
+    float* row = w + (size_t)(row0_local + r) * ld;
+    if (j < n) row[j] = 2.0f * (float)((j < i ? j : i) + 1);
+    if (j == 0) row[ycol] = (float)i;
+}
+void launch_init_fixture(float* w, int ld, int row0_local, int g0, int nrows, int n, int ycol, cudaStream_t s)
+{
+    if (nrows <= 0) return;
+    dim3 grid((n + 255) / 256, nrows);
+    init_fixture_kernel<<<grid, 256, 0, s>>>(w, ld, row0_local, g0, nrows, n, ycol);
+    ++g_launch_count;
+}
+
 void launch_set_column(float* w, int ld, int col, const float* src, int nrows, cudaStream_t s)
 {
     if (nrows <= 0) return;

@@ -27,6 +27,7 @@ static gauss_cuda_ctx *ctx;
 static gauss_cuda_stats stats;
 static int g_mode = GAUSS_CUDA_MODE_3XTF32;
 static int g_refine = 0;          /* -r: double-precision answers through gauss_cuda_solve_refined */
+static int g_devinit = 0;         /* -d: initMatrix generated on the GPU (fixture only): no host fill, no upload */
 static gauss_cuda_refine_info rinfo;
 
 static void die_on(int status, const char *where)
@@ -53,6 +54,11 @@ void allocate_memory(int size)
 
 void initMatrix(int nsize)
 {
+    if (g_devinit) {                           /* same values (gauss_internal_input.c:50-60), written by a kernel */
+        die_on(gauss_cuda_init_matrix_device(ctx), "gauss_cuda_init_matrix_device");
+        for (int i = 0; i < nsize; ++i) swap[i] = i;
+        return;
+    }
     gauss_host_init_matrix(matrix[0], B, nsize);
     for (int i = 0; i < nsize; ++i) swap[i] = i;
 }
@@ -68,9 +74,11 @@ void initialize_inputs(int nsize, unsigned seed)
 void computeGauss(int nsize)
 {
     size_t n = (size_t)nsize;
-    for (size_t i = 0; i < n * n; ++i) A32[i] = (float)matrix[0][i];
-    for (size_t i = 0; i < n; ++i) B32[i] = (float)B[i];
-    die_on(gauss_cuda_upload(ctx, A32, B32), "gauss_cuda_upload");
+    if (!g_devinit) {
+        for (size_t i = 0; i < n * n; ++i) A32[i] = (float)matrix[0][i];
+        for (size_t i = 0; i < n; ++i) B32[i] = (float)B[i];
+        die_on(gauss_cuda_upload(ctx, A32, B32), "gauss_cuda_upload");
+    }
     die_on(gauss_cuda_compute_gauss(ctx, &stats), "gauss_cuda_compute_gauss");
 }
 
@@ -100,23 +108,25 @@ void gauss(int nsize)
 
 static void usage(const char *p)
 {
-    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v] [-r]   (reference form)\n"
+    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v] [-r] [-d]   (reference form)\n"
            "       %s N [seed]                                               (seeded form)\n"
            "  -m 0 = tcgen05 3xTF32 (default), 1 = FFMA;  -v prints B[i] C[i] like VERIFY;\n"
-           "  -r = double-precision answers (FP32 elimination + iterative refinement)\n", p, p);
+           "  -r = double-precision answers (FP32 elimination + iterative refinement)\n"
+           "  -d = initMatrix on the GPU (no host fill, no upload; fixture form only)\n", p, p);
 }
 
 int main(int argc, char *argv[])
 {
     int nsize = 2048, verify = 0, seeded = 0, opt;
     unsigned seed = 1;
-    while ((opt = getopt(argc, argv, "hs:t:m:vr")) != -1) {
+    while ((opt = getopt(argc, argv, "hs:t:m:vrd")) != -1) {
         switch (opt) {
             case 's': { int s = atoi(optarg); if (s > 0) nsize = s; else fprintf(stderr, "Entered size is negative, hence using the default (%d)\n", 2048); } break;
             case 't': if (atoi(optarg) <= 0) { fprintf(stderr, "Error: Threads count should be a natural number. \n"); return 0; } break;
             case 'm': g_mode = atoi(optarg) ? GAUSS_CUDA_MODE_FFMA : GAUSS_CUDA_MODE_3XTF32; break;
             case 'v': verify = 1; break;
             case 'r': g_refine = 1; break;
+            case 'd': g_devinit = 1; break;
             case 'h': usage(argv[0]); return 0;
             default:  usage(argv[0]); return 1;
         }
@@ -128,6 +138,7 @@ int main(int argc, char *argv[])
         if (optind + 1 < argc) seed = (unsigned)strtoul(argv[optind + 1], NULL, 10);
     }
 
+    if (g_devinit && (seeded || g_refine)) { fprintf(stderr, "-d applies to the built-in fixture in FP32 only\n"); return 1; }
     printf("\nMatrix Size: %d ; Threads: %d\n", nsize, 1);
     allocate_memory(nsize);
 

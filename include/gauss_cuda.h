@@ -105,6 +105,10 @@ int gauss_cuda_download(gauss_cuda_ctx *ctx, float *X, float *B_out);
 
 /* The two halves separately, as the reference exposes them: computeGauss
  * (gauss_internal_input.c:118-138) then solveGauss (:144-159), on the resident system. */
+/* initMatrix(nsize) (gauss_internal_input.c:50-60: matrix[i][j] = 2 (min(i,j)+1), B[i] = i) generated on the device,
+ * in place of gauss_host_init_matrix + gauss_cuda_upload: the fixture never exists on the host, so the reference's
+ * timed window (init + elimination, :211-217) carries no 4 n^2-byte upload.  Every rank of a group fills its own rows. */
+int gauss_cuda_init_matrix_device(gauss_cuda_ctx *ctx);
 int gauss_cuda_compute_gauss(gauss_cuda_ctx *ctx, gauss_cuda_stats *st);
 int gauss_cuda_solve_gauss(gauss_cuda_ctx *ctx, gauss_cuda_stats *st);
 

@@ -40,6 +40,24 @@ def test_fixture_known_answer_bit_exact(n, mode):
 
 
 @pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("n", [5, 129, 1000, 2048])
+def test_fixture_generated_on_the_device(n, mode):
+    # gauss_cuda_init_matrix_device writes initMatrix's values (gauss_internal_input.c:50-60) with a kernel: the
+    # result must be what the host fill + upload gives, bit for bit, and the known answer
+    A, B = pkg.initMatrix(n)
+    with pkg.GaussCuda(n, mode=mode) as g:
+        g.initMatrix_device()
+        g.solve_resident()
+        X, Bafter = g.download(want_b_after=True)
+        g.upload(A, B)
+        g.solve_resident()
+        X2, B2 = g.download(want_b_after=True)
+    wx, wb = fixture_answer(n)
+    assert np.array_equal(X, wx) and np.array_equal(Bafter, wb)
+    assert np.array_equal(X, X2) and np.array_equal(Bafter, B2)
+
+
+@pytest.mark.parametrize("mode", MODES)
 def test_fixture_known_answer_at_scale(mode):
     # the same known answer holds for ANY n (gauss_internal_input.c:45-48) and the fixture is exact in FP32 and TF32:
     # a bit-exact check at a size where the CPU oracle would need minutes (3 outer blocks of 512, 64 inner blocks)
