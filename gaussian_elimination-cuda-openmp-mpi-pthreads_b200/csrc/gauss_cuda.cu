@@ -176,6 +176,7 @@ struct gauss_cuda_ctx {
     cudaStream_t s_main = nullptr, s_comm = nullptr;
     cudaEvent_t ev_ready[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_free[2] = {nullptr, nullptr};
     cudaEvent_t ev_diag[2] = {nullptr, nullptr}, ev_cols[2] = {nullptr, nullptr}, ev_p2[2] = {nullptr, nullptr};
+    cudaEvent_t ev_rdiag[2] = {nullptr, nullptr};   // owner: the kb x kb diagonal region of the panel is final (in-panel chain done)
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool trace = false;                 // GAUSS_CUDA_TRACE=1: per-phase timestamps of the multi-GPU main stream
     std::vector<cudaEvent_t> tr_ev;     // 6 per outer block
@@ -274,8 +275,11 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     const bool dist_fork = world > 1 && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0);
     if ((world == 1 && !(getenv("GAUSS_CUDA_INNER_FORK") && atoi(getenv("GAUSS_CUDA_INNER_FORK")) == 0)) || dist_fork) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_side, cudaStreamNonBlocking);
-        if (world == 1 && c->wide_split) {
-            if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_wide, cudaStreamNonBlocking);
+        if (c->wide_split) {
+            int lo_p = 0, hi_p = 0;
+            cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p);
+            // multi-GPU: the wide part of the panel factorisation belongs to the (priority) panel path
+            if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->s_wide, cudaStreamNonBlocking, world > 1 ? hi_p : lo_p);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_wide, cudaEventDisableTiming);
         }
         for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_inner[i], cudaEventDisableTiming);
@@ -296,6 +300,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
             e = cudaEventCreateWithFlags(&c->ev_ready[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_done[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_diag[i], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_rdiag[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_cols[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_p2[i], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_free[i], cudaEventDisableTiming);
@@ -377,6 +382,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
         if (c->ev_ready[i]) cudaEventDestroy(c->ev_ready[i]);
         if (c->ev_done[i]) cudaEventDestroy(c->ev_done[i]);
         if (c->ev_diag[i]) cudaEventDestroy(c->ev_diag[i]);
+        if (c->ev_rdiag[i]) cudaEventDestroy(c->ev_rdiag[i]);
         if (c->ev_cols[i]) cudaEventDestroy(c->ev_cols[i]);
         if (c->ev_p2[i]) cudaEventDestroy(c->ev_p2[i]);
         if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
@@ -468,7 +474,8 @@ struct StepBufs {            // the stream a piece runs on and the split-L buffe
 };
 
 // P1: factor the row panel of outer block K in place on its owner.
-static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo, const StepBufs& sb)
+static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo, const StepBufs& sb,
+                        cudaStream_t sw = nullptr, cudaEvent_t ev_in = nullptr)
 {
     cudaStream_t s = sb.s;
     const int ld = c->ld, NB = c->NB, np = c->np;
@@ -476,23 +483,48 @@ static int panel_factor(gauss_cuda_ctx* c, int K, float* ub_hi, float* ub_lo, co
     const int k0 = K * NB, kb = blk_rows(c, K), ninner = kb / kNb;
     const int lrow = blk_local_row(c, K);
     float* P = c->W + (size_t)lrow * ld;
+    // split at the right edge of the panel (as in outer_step): the in-panel chain -- all that the kb x kb diagonal
+    // region, and therefore the first broadcast and every rank's P2, depend on -- stays on `s`; the U-row solve and
+    // the rank-128 update right of the panel follow on `sw`, one inner block behind.  ev_in fires when the diagonal
+    // region is final; on return `s` has joined `sw` (the whole panel is done in stream order).
+    const bool split = sw != nullptr && sw != s && ninner >= 2 && ninner <= 8;
+    const int csplit = k0 + kb;
     for (int j = 0; j < ninner; ++j) {
         const int kk = k0 + j * kNb, r = j * kNb;
-        launch_diag_factor(P + (size_t)r * ld + kk, ld, kk, c->status, s);
+        float* D = P + (size_t)r * ld + kk;
+        launch_diag_factor(D, ld, kk, c->status, s);
         const int mrem = kb - (r + kNb);
-        // U-row solve over the full width and L-col solve of the panel rows below, one launch (both only need the factor)
-        launch_urow_lcol(P + (size_t)r * ld + kk, ld,
-                         P + (size_t)r * ld + kk + kNb, ld, np + 1 - (kk + kNb),
+        // U-row solve and L-col solve of the panel rows below, one launch (both only need the factor)
+        launch_urow_lcol(D, ld,
+                         D + kNb, ld, split ? csplit - (kk + kNb) : np + 1 - (kk + kNb),
                          tc ? ub_hi + (size_t)(kk + kNb) * NB : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB : nullptr, NB, r,
                          P + (size_t)(r + kNb) * ld + kk, ld, mrem,
                          tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB : nullptr, NB, r, s);
+        if (split) {
+            CK(cudaEventRecord(c->ev_inner[j], s));
+            CK(cudaStreamWaitEvent(sw, c->ev_inner[j], 0));
+            launch_urow(D, ld, P + (size_t)r * ld + csplit, ld, np + 1 - csplit,
+                        tc ? ub_hi + (size_t)csplit * NB : nullptr, tc ? ub_lo + (size_t)csplit * NB : nullptr, NB, r, sw);
+            if (mrem > 0) {
+                int rc = gemm_update(c, sw, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + csplit, ld,
+                                     tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
+                                     tc ? ub_hi + (size_t)csplit * NB + r : nullptr, tc ? ub_lo + (size_t)csplit * NB + r : nullptr,
+                                     P + (size_t)(r + kNb) * ld + csplit, mrem, ld - csplit, kNb);
+                if (rc) return rc;
+            }
+        }
         if (mrem > 0) {
-            int rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, P + (size_t)r * ld + kk + kNb, ld,
+            int rc = gemm_update(c, s, P + (size_t)(r + kNb) * ld + kk, ld, D + kNb, ld,
                                  tc ? sb.la_hi + (size_t)(lrow + r + kNb) * NB + r : nullptr, tc ? sb.la_lo + (size_t)(lrow + r + kNb) * NB + r : nullptr,
                                  tc ? ub_hi + (size_t)(kk + kNb) * NB + r : nullptr, tc ? ub_lo + (size_t)(kk + kNb) * NB + r : nullptr,
-                                 P + (size_t)(r + kNb) * ld + kk + kNb, mrem, ld - (kk + kNb), kNb);
+                                 P + (size_t)(r + kNb) * ld + kk + kNb, mrem, split ? csplit - (kk + kNb) : ld - (kk + kNb), kNb);
             if (rc) return rc;
         }
+    }
+    if (ev_in) CK(cudaEventRecord(ev_in, s));
+    if (split) {
+        CK(cudaEventRecord(c->ev_wide, sw));
+        CK(cudaStreamWaitEvent(s, c->ev_wide, 0));
     }
     return GAUSS_CUDA_OK;
 }
@@ -823,16 +855,19 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         float* bufd = c->pbuf[b];
         float* bufu = c->pbuf[b] + (size_t)kb * kb;
         CK(cudaStreamWaitEvent(sc, c->ev_free[b], 0));            // last readers of pbuf[b] are done
+        const float* P = c->W + (size_t)blk_local_row(c, K) * ld + k0;
         if (owner_of(K) == c->rank) {
-            CK(cudaStreamWaitEvent(sc, c->ev_ready[b], 0));       // P1(K) finished
-            const float* P = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+            CK(cudaStreamWaitEvent(sc, c->ev_rdiag[b], 0));       // the in-panel chain of P1(K) finished: the diagonal region is final
             CK(cudaMemcpy2DAsync(bufd, (size_t)kb * sizeof(float), P, (size_t)ld * sizeof(float),
                                  (size_t)kb * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
-            CK(cudaMemcpy2DAsync(bufu, (size_t)ldu * sizeof(float), P + kb, (size_t)ld * sizeof(float),
-                                 (size_t)ldu * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
         }
         NK(g_nccl.Broadcast(bufd, bufd, (size_t)kb * kb, ncclFloat, owner_of(K), c->comm, sc));
         CK(cudaEventRecord(c->ev_diag[b], sc));
+        if (owner_of(K) == c->rank) {
+            CK(cudaStreamWaitEvent(sc, c->ev_ready[b], 0));       // all of P1(K) finished
+            CK(cudaMemcpy2DAsync(bufu, (size_t)ldu * sizeof(float), P + kb, (size_t)ld * sizeof(float),
+                                 (size_t)ldu * sizeof(float), kb, cudaMemcpyDeviceToDevice, sc));
+        }
         NK(g_nccl.Broadcast(bufu, bufu, (size_t)kb * ldu, ncclFloat, owner_of(K), c->comm, sc));
         if (owner_of(K) != c->rank) c->bcast_bytes += (double)kb * (kb + ldu) * sizeof(float);
         CK(cudaEventRecord(c->ev_done[b], sc));
@@ -843,7 +878,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         const int b = K & 1;
         const PanelRef pr = panel_ref(K);
         if (owner_of(K) == c->rank) {
-            CK(cudaStreamWaitEvent(st, c->ev_ready[b], 0));
+            CK(cudaStreamWaitEvent(st, c->ev_rdiag[b], 0));       // the owner's P2 needs the diagonal region only
         } else {
             CK(cudaStreamWaitEvent(st, c->ev_diag[b], 0));
             if (tc) rebuild_split_u(c, K, pr, true, st);
@@ -856,7 +891,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
     CK(cudaEventRecord(c->ev_free[1], s));
     if (owner_of(0) == c->rank) {
         const StepBufs sb0{s, c->la_hi[0], c->la_lo[0]};
-        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sb0))) return rc;
+        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sb0, c->s_wide, c->ev_rdiag[0]))) return rc;
         CK(cudaEventRecord(c->ev_ready[0], s));
     }
     if ((rc = enqueue_bcast(0))) return rc;
@@ -872,7 +907,10 @@ static int factor_lookahead(gauss_cuda_ctx* c)
             CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // the U12 region has arrived
             mark(1);
             if (tc) rebuild_split_u(c, K, pr, false, s);
-        } else mark(1);
+        } else {
+            CK(cudaStreamWaitEvent(s, c->ev_ready[b], 0));        // all of P1(K), the part right of the panel included
+            mark(1);
+        }
         mark(2);
         const int l0 = first_local_block_after(c, K) * NB;
         if (K + 1 >= c->nblk) {                                   // last block: nothing below it
@@ -890,7 +928,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
                 CK(cudaStreamWaitEvent(sp, c->ev_fork[b], 0));
             }
             const StepBufs sbp{sp, c->la_hi[b ^ 1], c->la_lo[b ^ 1]};
-            if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbp))) return rc;
+            if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbp, sp != s ? c->s_wide : nullptr, c->ev_rdiag[b ^ 1]))) return rc;
             CK(cudaEventRecord(c->ev_ready[b ^ 1], sp));
             l1 = l0 + rows_next;
         }
