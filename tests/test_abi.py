@@ -85,6 +85,21 @@ def test_block_cyclic_ownership_partitions_rows(n, nb, world):
             assert pkg.block_owner(int(g) // min(nb, npad), world) == r
 
 
+def test_auto_outer_block_rule():
+    # host mirror of ctx_create's choice (the GPU suite checks it against stats.nb_outer); bench.py and multi-GPU callers
+    # place rows with it, so it must be a multiple of the inner block, never exceed the padded order, and keep the
+    # measured break points
+    for n in (1, 100, 2048, 4000, 4096, 8191, 8192, 16384, 24576, 32768):
+        for mode in (pkg.MODE_3XTF32, pkg.MODE_FFMA):
+            for world in (1, 2, 8):
+                nb = pkg.auto_outer_block(n, mode, world)
+                assert nb % 128 == 0 and 128 <= nb <= pkg.padded_order(n)
+    assert pkg.auto_outer_block(2048) == 128 and pkg.auto_outer_block(4096) == 256
+    assert pkg.auto_outer_block(8192) == 512 and pkg.auto_outer_block(16384) == 512
+    assert pkg.auto_outer_block(32768) == 1024 and pkg.auto_outer_block(32768, world=8) == 512
+    assert pkg.auto_outer_block(32768, pkg.MODE_FFMA) == 128 and pkg.auto_outer_block(32768, pkg.MODE_FFMA, 4) == 256
+
+
 def test_harness_cli_help_and_missing_gpu():
     exe = os.path.join(ROOT, "harness", "gauss_main")
     if not os.path.exists(exe):
