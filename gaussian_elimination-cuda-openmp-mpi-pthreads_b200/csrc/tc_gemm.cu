@@ -672,6 +672,7 @@ static thread_local int t_max_tiles = 0;
 static int g_dynamic = 1;            // GAUSS_CUDA_TC_STATIC=1 falls back to static round-robin tiles
 static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
 static int g_pair = 1;               // GAUSS_CUDA_TC_PAIR=0 switches the CTA-pair kernel off
+static int g_pair_min_tiles = 0;     // GAUSS_CUDA_TC_PAIR_MIN_TILES: pair tiles from which a launch uses it (0: two rounds)
 static thread_local bool t_pair_ok = true;   // callers that need the dynamic tile scheduler (multi-GPU) veto it
 
 bool tc_available()
@@ -696,6 +697,8 @@ int tc_setup_device()
     g_dynamic = (st && atoi(st)) ? 0 : 1;
     const char* pr = getenv("GAUSS_CUDA_TC_PAIR");
     g_pair = pr ? (atoi(pr) ? 1 : 0) : 1;
+    const char* pm = getenv("GAUSS_CUDA_TC_PAIR_MIN_TILES");
+    g_pair_min_tiles = pm ? atoi(pm) : 0;
     const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
     if (rs) g_reserve_sms = atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs));
     int dev = 0;
@@ -803,7 +806,7 @@ int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, co
     if (m <= 0 || n <= 0 || k <= 0) return 0;
     if (!g_encode || (k % 32) != 0) return (int)cudaErrorInvalidValue;
     if (g_pair && t_pair_ok && g_variant == 0 &&
-        ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN) >= 2 * (g_num_sms / 2))
+        ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN) >= (g_pair_min_tiles > 0 ? g_pair_min_tiles : 2 * (g_num_sms / 2)))
         return launch_pair(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
     if (g_variant == 1) return launch_variant<16, 4>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
     return launch_variant<32, 2>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
