@@ -1,5 +1,6 @@
 // libgauss_cuda.so -- the C ABI (include/gauss_cuda.h) and the host-side schedule of the blocked
-// no-pivot LU.  The arithmetic lives in lu_simt.cu (FFMA kernels) and tc_gemm.cu (tcgen05 tile engine).
+// no-pivot LU.  The arithmetic lives in tc_gemm.cu (tcgen05 tile engine: trailing update), lu_panel.cu (diagonal
+// factor, panel solves), lu_simt.cu (FFMA variant, back substitution, helpers) and lu_pivot.cu (pivoting panel).
 //
 // Algorithm (two-level right-looking Crout LU on the augmented matrix [A | b], FP32):
 //   outer block K = rows/cols [k0, k0+kb), kb <= NB (NB a multiple of 128), owner rank = K mod world
@@ -12,6 +13,9 @@
 //   P3 (all)    local rows below, columns right of the panel:  A22 -= L21 * U12   (K = kb)
 // which reproduces computeGauss (gauss_internal_input.c:118-138) up to rounding order; back
 // substitution (solveGauss :144-159) runs block-wise from the last outer block up.
+// Schedules: factor_single (one GPU, captured into a CUDA graph; P2 and the wide part of P1 on side streams),
+// factor_streamed (one GPU, host data: upload overlapped, up-looking across row chunks), factor_lookahead
+// (multi-GPU pipeline), factor_pivot (external-input variant), gauss_cuda_solve_refined (double-precision answers).
 #include "gauss_cuda.h"
 #include "gauss_internal.cuh"
 

@@ -1,10 +1,10 @@
 // Panel kernels of the blocked no-pivot LU (the latency-critical part of computeGauss,
 // gauss_internal_input.c:118-138): the 128x128 diagonal-block factor and the two triangular
-// panel solves.  All three work on 32-wide sub-blocks so that the only strictly sequential part
-// is 32 pivot steps at a time; everything else is small dense block products spread over 256 threads.
+// panel solves.  The solves work on 32-wide sub-blocks; their block products run as FP32 FFMAs
+// (sections 2-3, FFMA mode) or as warp-level TF32 MMAs (section 4, 3xTF32 mode).
 //
-//   diag_factor  A11 = L11*U11 in shared memory (Crout: U unit upper, L carries the pivots;
-//                getPivot :100-111 scales row i by 1/pivot, computeGauss :129-136 eliminates)
+//   diag_factor  A11 = L11*U11 in registers, two pivots per barrier (Crout: U unit upper, L carries the
+//                pivots; getPivot :100-111 scales row i by 1/pivot, computeGauss :129-136 eliminates)
 //   urow         U12 = L11^-1 * A12      (the part of rows i right of the diagonal block, :132-134)
 //   lcol         L21 = A21 * U11^-1      (the multipliers a_ji of the rows below, :130)
 // urow/lcol invert the four 32x32 diagonal sub-blocks once per CTA (one warp each) and then run
