@@ -1311,8 +1311,12 @@ extern "C" int gauss_cuda_solve_refined(gauss_cuda_ctx* c, const double* A, cons
                                         int max_iters, double tol, gauss_cuda_refine_info* info)
 {
     if (!c || !A || !B || !X || max_iters < 0) return GAUSS_CUDA_BAD_ARG;
-    if (c->world != 1 || c->pivot) {
-        snprintf(g_err, sizeof g_err, "gauss_cuda_solve_refined: single-GPU contexts without pivoting only");
+    if (c->world != 1) {
+        snprintf(g_err, sizeof g_err, "gauss_cuda_solve_refined: single-GPU contexts only");
+        return GAUSS_CUDA_BAD_ARG;
+    }
+    if (c->pivot && (size_t)c->np * sizeof(float) > 200 * 1024) {
+        snprintf(g_err, sizeof g_err, "gauss_cuda_solve_refined with pivoting: padded order %d exceeds 51200", c->np);
         return GAUSS_CUDA_BAD_ARG;
     }
     CK(cudaSetDevice(c->device));
@@ -1340,21 +1344,27 @@ extern "C" int gauss_cuda_solve_refined(gauss_cuda_ctx* c, const double* A, cons
     CK(cudaEventRecord(c->ev[4], s));
     rc = finish_stats(c, nullptr, true, true, true, false);
     if (rc) return rc;                                                      // zero pivot: nothing to refine
+    if (c->pivot)                            // P A = L U with L in final row order: the earlier L columns get the later panels' swaps
+        for (int k0 = kNb; k0 < np; k0 += kNb) launch_laswp_left(c->W, ld, k0, c->ipiv, s);
     double h[2] = {0.0, 0.0}, prev = 0.0;
     int it = 0, converged = 0;
     for (; it < max_iters; ++it) {
         launch_residual_f64(c->A64, x64, b64, r64, rf, n, s);
+        if (c->pivot) launch_apply_pivots_vec(rf, c->ipiv, np, s);           // d = U^-1 L^-1 P r
         launch_trsv_factor_solve(c->W, ld, np, rf, yf, true, c->trsv_ctrl, s);
         launch_trsv_factor_solve(c->W, ld, np, yf, df, false, c->trsv_ctrl, s);
         launch_refine_update(x64, df, n, norms, s);
         CK(cudaMemcpyAsync(h, norms, sizeof h, cudaMemcpyDeviceToHost, s));
         CK(cudaStreamSynchronize(s));
         const double rel = h[1] > 0.0 ? h[0] / h[1] : h[0];
-        if (!(rel == rel) || (it > 0 && rel > prev)) {                       // NaN or growing corrections: not contracting
-            ++it; prev = rel; break;
+        if (rel <= tol) { ++it; prev = rel; converged = 1; break; }
+        if (!(rel == rel) || (it > 0 && rel > 0.5 * prev)) {
+            // the corrections no longer halve: either the iteration does not contract (cond(A) 2^-24 too close to 1),
+            // or -- far below FP32 accuracy -- it has reached what double residuals can resolve for this matrix
+            // (the reference's own error on orsreg_1 is 2e-10): 2 = stagnated at working precision, 0 = failed
+            ++it; converged = (rel == rel && rel <= 1e-7) ? 2 : 0; prev = rel; break;
         }
         prev = rel;
-        if (rel <= tol) { ++it; converged = 1; break; }
     }
     launch_residual_f64(c->A64, x64, b64, r64, rf, n, s);                   // the residual of the returned x, for info
     CK(cudaGetLastError());

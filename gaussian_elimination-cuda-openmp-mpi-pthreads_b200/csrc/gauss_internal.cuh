@@ -70,6 +70,8 @@ int  tc_setup_device();       // same for the tile engine; returns a GAUSS_CUDA_
 // Factors the panel W[k0.., k0..k0+128) of an [np x ld] single-GPU system with row interchanges
 // (gauss_external_input.c:123-148, 161-181); see lu_pivot.cu.  la_* (may be null): split of the rows
 // below the diagonal block, la[(i-128)*ldla + c].
+void launch_laswp_left(float* W, int ld, int k0, const int* ipiv, cudaStream_t s);      // panel k0's swaps on the columns left of it
+int  launch_apply_pivots_vec(float* v, const int* ipiv, int np, cudaStream_t s);       // v <- P v; non-zero: np too large (> 51200)
 void launch_panel_pivot(float* W, int ld, int np, int k0, float* pt, int mp, int* ipiv, int* status,
                         float* la_hi, float* la_lo, int ldla, cudaStream_t s);
 

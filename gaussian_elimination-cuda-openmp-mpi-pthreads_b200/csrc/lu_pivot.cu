@@ -170,4 +170,47 @@ void launch_panel_pivot(float* W, int ld, int np, int k0, float* pt, int mp, int
     }
 }
 
+// The interchanges of panel k0 applied to the columns LEFT of it (the L columns factored earlier).  The elimination
+// itself never needs this -- like the reference it only swaps row tails (gauss_external_input.c:139-146) -- but a
+// solve with the stored factors for a NEW right-hand side does: afterwards P A = L U holds with L in final row order.
+void launch_laswp_left(float* W, int ld, int k0, const int* ipiv, cudaStream_t s)
+{
+    if (k0 <= 0) return;
+    laswp_kernel<<<(k0 + 255) / 256, 256, 0, s>>>(W, ld, k0, ipiv, k0);
+    ++g_launch_count;
+}
+
+// v <- P v: every interchange of the factorisation, in pivot order, applied to a vector of np floats.  One CTA; the
+// vector sits in shared memory while one thread walks the pivot list (the swaps are inherently sequential).
+__global__ void __launch_bounds__(1024)
+apply_pivots_vec_kernel(float* __restrict__ v, const int* __restrict__ ipiv, int np)
+{
+    extern __shared__ float sv[];
+    for (int i = threadIdx.x; i < np; i += blockDim.x) sv[i] = v[i];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 0; k < np; ++k) {
+            const int p = ipiv[k];
+            if (p != k) { const float a = sv[k]; sv[k] = sv[p]; sv[p] = a; }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < np; i += blockDim.x) v[i] = sv[i];
+}
+int launch_apply_pivots_vec(float* v, const int* ipiv, int np, cudaStream_t s)
+{
+    const size_t bytes = (size_t)np * sizeof(float);
+    if (bytes > 200 * 1024) return 1;                       // the caller reports the limit
+    static bool configured[16] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 16 && !configured[dev]) {
+        cudaFuncSetAttribute(apply_pivots_vec_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        configured[dev] = true;
+    }
+    apply_pivots_vec_kernel<<<1, 1024, bytes, s>>>(v, ipiv, np);
+    ++g_launch_count;
+    return 0;
+}
+
 } // namespace gb200

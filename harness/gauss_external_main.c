@@ -8,6 +8,8 @@
  *   "\nMatrix File: %s; Matrix Size: %d ; Threads: %d\n" (:234), "Time:  %f seconds\n" (:244), "Error: %e\n" (:253);
  * a missing file prints "The matrix file open error" and exits -1 (:42-45), a singular matrix prints
  * "The matrix is singular" on stderr and exits -1 (:133-136).  Elimination uses partial pivoting.
+ * Extra: a trailing  -r  solves in the reference's own precision (FP32 pivoted elimination + iterative refinement
+ * with double residuals, gauss_cuda_solve_refined); the timer then covers the whole refined solve.
  */
 #include <stdio.h>
 #include <stdlib.h>
@@ -64,6 +66,8 @@ void solveGauss(int nsize)
 
 int main(int argc, char *argv[])
 {
+    int refine = 0;
+    if (argc >= 3 && argv[argc - 1][0] == '-' && argv[argc - 1][1] == 'r' && argv[argc - 1][2] == 0) { refine = 1; --argc; }
     if (argc != 2 && argc != 3) {
         fprintf(stderr, "usage: %s <matrixfile> <number_of_threads (optional)>\n", argv[0]);
         exit(-1);
@@ -87,10 +91,12 @@ int main(int argc, char *argv[])
     fail(gauss_cuda_set_pivoting(ctx, 1), "gauss_cuda_set_pivoting");
 
     struct timeval start, finish;
+    gauss_cuda_refine_info info;
     gettimeofday(&start, 0);
-    computeGauss(nsize);
+    if (refine) fail(gauss_cuda_solve_refined(ctx, matrix[0], R, X, 30, 1e-14, &info), "gauss_cuda_solve_refined");
+    else computeGauss(nsize);
     gettimeofday(&finish, 0);
-    solveGauss(nsize);
+    if (!refine) solveGauss(nsize);
     fprintf(stdout, "Time:  %f seconds\n", (finish.tv_sec - start.tv_sec) + (finish.tv_usec - start.tv_usec) * 0.000001);
 
     double error = 0.0;
@@ -99,6 +105,8 @@ int main(int argc, char *argv[])
         if (error < e) error = e;
     }
     fprintf(stdout, "Error: %e\n", error);
+    if (refine) fprintf(stdout, "Refinement: %d sweeps, %s, last correction %.2e\n", info.iterations,
+                        info.converged == 1 ? "converged" : (info.converged == 2 ? "stagnated at working precision" : "NOT converged"), info.last_correction);
     gauss_cuda_free(ctx);
     return 0;
 }

@@ -155,7 +155,7 @@ int main(int argc, char *argv[])
     const double flop = 2.0 / 3.0 * (double)nsize * nsize * nsize;
     if (g_refine)
         printf("GPU FP32 solve incl. upload: %.6f s, refinement: %d sweeps in %.6f s (%s, last correction %.2e, residual %.2e)\n",
-               rinfo.factor_s, rinfo.iterations, rinfo.refine_s, rinfo.converged ? "converged" : "NOT converged",
+               rinfo.factor_s, rinfo.iterations, rinfo.refine_s, rinfo.converged == 1 ? "converged" : (rinfo.converged == 2 ? "stagnated at working precision" : "NOT converged"),
                rinfo.last_correction, rinfo.residual_inf);
     else
         printf("GPU elimination: %.6f s (%.1f GFLOP/s, 2/3 N^3), back substitution: %.6f s, mode %s, outer block %d\n",

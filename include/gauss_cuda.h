@@ -131,13 +131,16 @@ int gauss_cuda_get_pivots(gauss_cuda_ctx *ctx, int *pivot_rows /* host, n */);
  * reference's accuracy by mixed-precision iterative refinement: A is rounded to FP32 and eliminated exactly as in
  * gauss_cuda_solve (computeGauss :118-141), then x is corrected in sweeps  r = b - A x  (double, on the device),
  * d = U^-1 L^-1 r  (the stored FP32 factors, two triangular solves -- solveGauss :144-159 and its forward
- * counterpart), x += d, until  max|d| <= tol * max|x|,  the corrections stop shrinking, or max_iters sweeps ran.
+ * counterpart), x += d, until  max|d| <= tol * max|x|,  the corrections stop halving, or max_iters sweeps ran.
  * Converges when cond(A) * 2^-24 is well below 1 (the reference's own inputs are); `converged` says whether the
- * tolerance was met.  A, B, X: host, n*n / n / n doubles.  Single-GPU contexts without pivoting only.
+ * tolerance was met.  A, B, X: host, n*n / n / n doubles.  Single-GPU contexts; with partial pivoting switched on
+ * (gauss_cuda_set_pivoting) the sweeps solve with P A = L U -- the external-input program in the reference's own
+ * precision (gauss_external_input.c prints Error: 4.8e-15 for jpwh_991) -- for padded orders up to 51200.
  * Device memory for the double copy of A (8 n^2 bytes) is allocated on the first call and kept by the context. */
 typedef struct gauss_cuda_refine_info {
     int iterations;            /* refinement sweeps done */
-    int converged;             /* 1: last max|d|/max|x| <= tol */
+    int converged;             /* 1: last max|d|/max|x| <= tol; 2: the corrections stopped halving below 1e-7, i.e. the
+                                * answer is as good as double residuals can make it for this matrix; 0: neither */
     double last_correction;    /* max|d| / max|x| of the last sweep */
     double residual_inf;       /* max_i |b - A x|_i of the returned x, in double */
     double factor_s;           /* upload + FP32 elimination + first back substitution, seconds */

@@ -89,10 +89,6 @@ def test_rejected_configurations():
     n = 64
     A, B, _ = pkg.initialize_inputs(n, 1)
     with pkg.GaussCuda(n) as g:
-        g.set_pivoting(True)
-        with pytest.raises(pkg.GaussCudaError):
-            g.gauss_refined(A, B)
-        g.set_pivoting(False)
         with pytest.raises(pkg.GaussCudaError):
             g.gauss_refined(A, B, max_iters=-1)
         A0 = A.copy()
