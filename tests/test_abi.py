@@ -109,3 +109,23 @@ def test_harness_cli_help_and_missing_gpu():
     if pkg.device_count() == 0:
         out = subprocess.run([exe, "-s", "64"], capture_output=True, text=True)
         assert out.returncode == 2 and "Matrix Size: 64" in out.stdout and "CUDA" in out.stderr
+
+
+def test_external_harness_parses_its_arguments_without_gpu(tmp_path):
+    # <matrixfile> [threads] [-r]: the reference's CLI (gauss_external_input.c:214-230) plus the refinement switch;
+    # without a GPU the program must get as far as the device context and stop there with the library's message
+    exe = os.path.join(ROOT, "harness", "gauss_external_main")
+    if not os.path.exists(exe):
+        pytest.skip("harness not built")
+    z = np.load(os.path.join(ROOT, "tests", "golden", "external_vectors.npz"))
+    path = tmp_path / "matrix_10.dat"
+    path.write_bytes(z["matrix_10_text"].tobytes())
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode != 0 and "usage" in out.stderr
+    out = subprocess.run([exe, str(path), "0"], capture_output=True, text=True)
+    assert out.returncode != 0 and "natural number" in out.stderr
+    if pkg.device_count() == 0:
+        for args in ([str(path)], [str(path), "4"], [str(path), "4", "-r"], [str(path), "-r"]):
+            out = subprocess.run([exe] + args, capture_output=True, text=True)
+            assert out.returncode == 2 and "Matrix Size: 10" in out.stdout and "CUDA" in out.stderr, (args, out.stderr)
+
