@@ -44,7 +44,7 @@ class GaussStats(C.Structure):
         ("mode", C.c_int), ("rank", C.c_int), ("world", C.c_int),
         ("kernel_launches", C.c_longlong),
         ("update_s", C.c_double), ("update_flops", C.c_double), ("update_launches", C.c_int),
-        ("overlapped_upload", C.c_int),
+        ("overlapped_upload", C.c_int), ("graph_replayed", C.c_int),
     ]
 
     def asdict(self):

@@ -26,6 +26,7 @@
 #include <string.h>
 #include <math.h>
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 using namespace gb200;
@@ -158,6 +159,7 @@ struct gauss_cuda_ctx {
     // (at N = 2048 the ~90 launches otherwise cost more host time than the GPU needs to run them)
     cudaGraphExec_t gexec = nullptr;
     bool capturing = false, graph_failed = false, use_graph = true;
+    bool last_graph = false;            // the last run_core replayed the captured graph (reported in gauss_cuda_stats)
     long long graph_launches = 0;
     int graph_upd_count = 0;
     bool pivot = false;         // partial pivoting (external-input variant)
@@ -1047,6 +1049,8 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
     o.zero_pivot_row = flag ? flag - 1 : -1;
     o.n = c->n; o.n_padded = c->np; o.nb_outer = c->NB; o.nb_inner = kNb; o.mode = c->mode; o.rank = c->rank; o.world = c->world;
     o.kernel_launches = g_launch_count;
+    o.graph_replayed = c->last_graph ? 1 : 0;
+    c->last_graph = false;
     o.update_s = 0.0; o.update_flops = 0.0; o.update_launches = 0;
     if (fac) {
         for (int i = 0; i < c->upd_count; ++i) {
@@ -1118,6 +1122,7 @@ static int core_body(gauss_cuda_ctx* c)
     if ((rc = snapshot_rhs(c))) return rc;
     if ((rc = backsub(c))) return rc;
     CK(rec_event(c, c->ev[3], s));
+    c->factored = false;                     // the RHS column now holds x: solveGauss must not run a second time
     return GAUSS_CUDA_OK;
 }
 
@@ -1151,7 +1156,8 @@ static int run_core(gauss_cuda_ctx* c)
         c->bcast_bytes = 0.0;
         CK(cudaGraphLaunch(c->gexec, s));
         g_launch_count += c->graph_launches;
-        c->factored = true;
+        c->factored = false;                 // elimination and back substitution both ran (see core_body)
+        c->last_graph = true;
         return GAUSS_CUDA_OK;
     }
     return core_body(c);
@@ -1193,6 +1199,7 @@ extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* 
         if ((rc = snapshot_rhs(c))) return rc;
         if ((rc = backsub(c))) return rc;
         CK(cudaEventRecord(c->ev[3], s));
+        c->factored = false;
     } else {
         if ((rc = upload_into(c, c->W, A, B))) return rc;
         if ((rc = run_core(c))) return rc;
@@ -1432,8 +1439,15 @@ extern "C" int gauss_cuda_download_factors(gauss_cuda_ctx* c, float* LU)
 struct MatmulScratch {            // per device, grown on demand, kept until process exit
     float* buf = nullptr;
     size_t bytes = 0;
+    // every call on a device shares `buf`; calls on different streams (or from different host threads) are put in
+    // order with this event -- the next call's stream waits for the previous call's kernels -- so they can never
+    // overwrite each other's operand copies (the reference's gpu_matmul<<<>>> launch has no such restriction either)
+    cudaEvent_t last_done = nullptr;
+    cudaStream_t last_stream = nullptr;
+    bool used = false;
 };
 static MatmulScratch g_mm[16];
+static std::mutex g_mm_mutex;
 
 static int mm_scratch(int dev, size_t bytes, float** out)
 {
@@ -1508,8 +1522,18 @@ extern "C" int matmul_cuda_device(const float* dA, const float* dB, float* dC, i
     }
     float* scratch = nullptr;
     const size_t need = matmul_scratch_bytes(n, mode);
-    if (need) { int rc = mm_scratch(dev, need, &scratch); if (rc) return rc; }
-    return matmul_on_device(dA, dB, dC, n, mode, scratch, (cudaStream_t)stream);
+    if (!need) return matmul_on_device(dA, dB, dC, n, mode, nullptr, (cudaStream_t)stream);
+    std::lock_guard<std::mutex> lock(g_mm_mutex);
+    MatmulScratch& sc = g_mm[dev & 15];
+    { int rc = mm_scratch(dev, need, &scratch); if (rc) return rc; }
+    if (!sc.last_done) CK(cudaEventCreateWithFlags(&sc.last_done, cudaEventDisableTiming));
+    if (sc.used && sc.last_stream != (cudaStream_t)stream) CK(cudaStreamWaitEvent((cudaStream_t)stream, sc.last_done, 0));
+    int rc = matmul_on_device(dA, dB, dC, n, mode, scratch, (cudaStream_t)stream);
+    if (rc) return rc;
+    CK(cudaEventRecord(sc.last_done, (cudaStream_t)stream));
+    sc.last_stream = (cudaStream_t)stream;
+    sc.used = true;
+    return GAUSS_CUDA_OK;
 }
 
 extern "C" int matmul_cuda(const float* A, const float* B, float* C, int n, int mode, double* kernel_s)
@@ -1573,22 +1597,29 @@ extern "C" int matmul_cuda_device_noalloc(const float* dA, const float* dB, floa
     if (gauss_cuda_device_count() < 1) { snprintf(g_err, sizeof g_err, "no CUDA device (no CPU fallback)"); return GAUSS_CUDA_CUDA_ERR; }
     int dev = 0;
     CK(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 16) return GAUSS_CUDA_BAD_ARG;
-    if (matmul_scratch_bytes(n, mode) > kNoAllocFloats * sizeof(float)) return GAUSS_CUDA_BAD_ARG;   // cannot happen for n <= 1024
-    if (!g_noalloc_addr[dev]) {
-        // first call on this device: one-time set-up (symbol address, kernel attributes, TMA encoder)
-        float* p = nullptr;
-        CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
-        simt_setup_device();
-        if (mode == GAUSS_CUDA_MODE_3XTF32 || tc_available()) {
-            int rc = tc_setup_device();
-            if (rc) return rc;
-        }
-        g_noalloc_addr[dev] = p;
+    if (dev < 0 || dev >= 16) {
+        snprintf(g_err, sizeof g_err, "matmul_cuda_device_noalloc: device ordinal %d is outside the 16 this library keeps set-up state for", dev);
+        return GAUSS_CUDA_BAD_ARG;
+    }
+    if (matmul_scratch_bytes(n, mode) > kNoAllocFloats * sizeof(float)) {   // cannot happen for n <= 1024
+        snprintf(g_err, sizeof g_err, "matmul_cuda_device_noalloc: scratch for n = %d does not fit the built-in array", n);
+        return GAUSS_CUDA_BAD_ARG;
     }
     if (mode == GAUSS_CUDA_MODE_3XTF32 && !tc_available()) {
         snprintf(g_err, sizeof g_err, "GAUSS_CUDA_MODE_3XTF32 needs an sm_100 device");
         return GAUSS_CUDA_CUDA_ERR;
+    }
+    if (!g_noalloc_addr[dev]) {
+        // first call on this device: one-time set-up (symbol address, kernel attributes, TMA encoder).  The tile
+        // engine's process-wide switches are left as they are when another caller has already set them up.
+        float* p = nullptr;
+        CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+        simt_setup_device();
+        if (tc_available()) {
+            int rc = tc_setup_device(/*reread_env=*/false);
+            if (rc) return rc;
+        }
+        g_noalloc_addr[dev] = p;
     }
     // Every region of the scratch that this call reads is written by this call first (the operand
     // splits include their zero K-padding; the padded FFMA path clears its operand copies), so the

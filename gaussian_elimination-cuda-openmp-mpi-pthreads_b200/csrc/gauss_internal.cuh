@@ -64,7 +64,8 @@ void launch_split_rowmajor(const float* src, int lds, float* hi, float* lo, int 
 void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, int rext, cudaStream_t s);
 void simt_setup_device();     // per-device dynamic shared memory opt-ins of the SIMT kernels
 void panel_setup_device();    // same for lu_panel.cu (called by simt_setup_device)
-int  tc_setup_device();       // same for the tile engine; returns a GAUSS_CUDA_* status
+int  tc_setup_device(bool reread_env = true);   // same for the tile engine; returns a GAUSS_CUDA_* status.  reread_env = false leaves the
+                                                // process-wide GAUSS_CUDA_TC_* switches alone once some caller has read them
 
 // ---- partial-pivoting panel (lu_pivot.cu) --------------------------------------------------
 // Factors the panel W[k0.., k0..k0+128) of an [np x ld] single-GPU system with row interchanges

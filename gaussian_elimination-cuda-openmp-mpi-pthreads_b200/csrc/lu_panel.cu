@@ -49,6 +49,12 @@ __device__ __forceinline__ float fast_rcp(float x)
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return fmaf(r, fmaf(-x, r, 1.0f), r);                 // one Newton step: full FP32 accuracy, exact for powers of two
 }
+// A pivot the elimination cannot divide by: zero, NaN, infinite, subnormal (rcp.approx.ftz flushes it to zero and
+// returns inf) or so large that its reciprocal is flushed to zero.  `r` is fast_rcp(p).
+__device__ __forceinline__ bool bad_pivot(float p, float r)
+{
+    return !(fabsf(p) >= 1.17549435e-38f) || !(fabsf(r) >= 1.17549435e-38f) || isinf(p) || isinf(r);
+}
 
 struct DiagSmem {
     float rowbuf[2][kNb];
@@ -85,7 +91,7 @@ __device__ __forceinline__ void diag_phase(float (&a)[8][8], DiagSmem& sm, const
         const float r = fast_rcp(piv);
         if (tx == kk && ty == kk) {
             sm.rinv[k] = r;
-            if (!(fabsf(piv) > 0.f) || isinf(piv)) atomicMin(&sm.first_bad, k);
+            if (bad_pivot(piv, r)) atomicMin(&sm.first_bad, k);
         }
         // only the first row/column group of the phase can still contain indices <= k
         float rv[8], lv[8];
@@ -137,8 +143,8 @@ __device__ __forceinline__ void diag_phase2(float (&a)[8][8], DiagSmem2& sm, con
         if (tx == kk && ty == kk) {
             sm.rinv[k] = r0;
             sm.rinv[k + 1] = r1;
-            if (!(fabsf(p0) > 0.f) || isinf(p0)) atomicMin(&sm.first_bad, k);
-            else if (!(fabsf(p1) > 0.f) || isinf(p1)) atomicMin(&sm.first_bad, k + 1);
+            if (bad_pivot(p0, r0)) atomicMin(&sm.first_bad, k);
+            else if (bad_pivot(p1, r1)) atomicMin(&sm.first_bad, k + 1);
         }
         // only the first row/column group of the phase can still contain indices <= k+1
         float u0[8], u1[8], l0[8], l1[8];

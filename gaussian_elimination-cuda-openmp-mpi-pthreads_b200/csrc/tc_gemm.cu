@@ -656,7 +656,6 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 static EncodeTiledFn g_encode = nullptr;
-static int g_variant = 0;            // 0: BK=32, 2 stages (128 B swizzle); 1: BK=16, 4 stages (64 B swizzle)
 static int g_num_sms = 0;
 // Scheduler slots: {tile counter, exit counter} pairs in a file-scope device array (zero at load, rearmed by
 // each launch's last CTA).  Launches rotate through the slots so that kernels in flight on different
@@ -669,7 +668,7 @@ static unsigned g_sched_next = 0;
 // on different streams can never share one); everyone else uses the library's ring.
 static thread_local int* t_sched_override = nullptr;
 static thread_local int t_max_tiles = 0;
-static int g_dynamic = 1;            // GAUSS_CUDA_TC_STATIC=1 falls back to static round-robin tiles
+constexpr int g_dynamic = 1;         // tiles come from the dynamic scheduler (static round-robin was measured and dropped)
 static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
 static int g_pair = 1;               // GAUSS_CUDA_TC_PAIR=0 switches the CTA-pair kernel off
 static int g_pair_min_tiles = 0;     // GAUSS_CUDA_TC_PAIR_MIN_TILES: pair tiles from which a launch uses it (0: two rounds)
@@ -683,7 +682,9 @@ bool tc_available()
     return major == 10;
 }
 
-int tc_setup_device()
+static bool g_env_read = false;
+
+int tc_setup_device(bool reread_env)
 {
     if (!g_encode) {
         void* fn = nullptr;
@@ -691,16 +692,15 @@ int tc_setup_device()
         if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn) return GAUSS_CUDA_CUDA_ERR;
         g_encode = (EncodeTiledFn)fn;
     }
-    const char* v = getenv("GAUSS_CUDA_TC_VARIANT");
-    if (v) g_variant = atoi(v) ? 1 : 0;
-    const char* st = getenv("GAUSS_CUDA_TC_STATIC");
-    g_dynamic = (st && atoi(st)) ? 0 : 1;
-    const char* pr = getenv("GAUSS_CUDA_TC_PAIR");
-    g_pair = pr ? (atoi(pr) ? 1 : 0) : 1;
-    const char* pm = getenv("GAUSS_CUDA_TC_PAIR_MIN_TILES");
-    g_pair_min_tiles = pm ? atoi(pm) : 0;
-    const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
-    if (rs) g_reserve_sms = atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs));
+    if (reread_env || !g_env_read) {       // context creation re-reads the switches (tests flip them); other callers leave them
+        const char* pr = getenv("GAUSS_CUDA_TC_PAIR");
+        g_pair = pr ? (atoi(pr) ? 1 : 0) : 1;
+        const char* pm = getenv("GAUSS_CUDA_TC_PAIR_MIN_TILES");
+        g_pair_min_tiles = pm ? atoi(pm) : 0;
+        const char* rs = getenv("GAUSS_CUDA_TC_RESERVE_SMS");
+        g_reserve_sms = rs ? (atoi(rs) < 0 ? 0 : (atoi(rs) > 64 ? 64 : atoi(rs))) : 0;
+        g_env_read = true;
+    }
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
@@ -710,7 +710,6 @@ int tc_setup_device()
         g_sched_addr[dev] = p;
     }
     cudaError_t e = cudaFuncSetAttribute(tc_gemm_kernel<32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<32, 2>::smem_bytes);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_gemm_kernel<16, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg<16, 4>::smem_bytes);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(tc_gemm_pair_kernel<32, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, TcCfg2<32, 3>::smem_bytes);
     return e == cudaSuccess ? GAUSS_CUDA_OK : GAUSS_CUDA_CUDA_ERR;
 }
@@ -805,10 +804,9 @@ int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, co
 {
     if (m <= 0 || n <= 0 || k <= 0) return 0;
     if (!g_encode || (k % 32) != 0) return (int)cudaErrorInvalidValue;
-    if (g_pair && t_pair_ok && g_variant == 0 &&
+    if (g_pair && t_pair_ok &&
         ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN) >= (g_pair_min_tiles > 0 ? g_pair_min_tiles : 2 * (g_num_sms / 2)))
         return launch_pair(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
-    if (g_variant == 1) return launch_variant<16, 4>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
     return launch_variant<32, 2>(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
 }
 

@@ -61,6 +61,10 @@ typedef struct {
      * otherwise).  h2d_s is then the time until the last chunk had arrived and factor_s (which contains the
      * waiting for chunks) overlaps it; results are bit-identical to the upload-first schedule. */
     int    overlapped_upload;
+    /* 1: the elimination + back substitution of this call ran as one replay of the context's captured CUDA graph
+     * (single GPU, no pivoting); 0: plain stream launches (multi-GPU, pivoting, the overlapped upload, GAUSS_CUDA_GRAPH=0,
+     * or graph capture failed on this context -- in which case every later call of the context stays on plain launches) */
+    int    graph_replayed;
 } gauss_cuda_stats;
 
 /* ---- Gaussian elimination ------------------------------------------------------------- */
@@ -162,7 +166,9 @@ int matmul_cuda(const float *A, const float *B, float *C, int n, int mode, doubl
 /* Replaces the launch gpu_matmul<<<grid, block>>>(d_A, d_B, d_C, nsize) (cuda_matmul.cu:155,
  * kernel :89-101): device pointers, C = A*B, asynchronous on `stream` (a cudaStream_t, NULL =
  * default stream).  Mode 3xTF32 keeps per-device scratch (split operand copies) that is
- * allocated on first use and grown on demand. */
+ * allocated on first use and grown on demand.  Calls on one device share that scratch: a call on a
+ * different stream than the previous one first waits (on the GPU, through an event) for the previous
+ * call's kernels, so concurrent streams and host threads get correct results but do not overlap. */
 int matmul_cuda_device(const float *dA, const float *dB, float *dC, int n, int mode, void *stream);
 
 /* Same multiply for callers that are not allowed to allocate device memory.  (No counterpart in the

@@ -268,3 +268,21 @@ def test_linearity_and_residual_at_scale(mode):
     assert ol.max_rel_error(X, xt) <= TOL
     assert ol.scaled_residual(A, B, X) <= 10.0
     assert np.max(np.abs(X2 - 2.0 * X)) <= 1e-5 * np.max(np.abs(X2))       # scaling b by 2 is exact in binary FP
+
+
+def test_north_star_generator_at_config4_size():
+    # BASELINE config 4 (N = 16384) on the harness's own srand/rand initialize_inputs (diagonally dominant, x = 1..n):
+    # the north_star's scaled residual ||Ax-b||inf / (||A||inf ||x||inf n eps) <= 10, and the solution norm-wise to
+    # 1e-3 (element-wise 1e-3 next to entries of size n is below FP32 resolution at this size, see above);
+    # the double-precision entry then has to reach the reference's accuracy element-wise
+    n = 16384
+    A, B, Xtrue = pkg.initialize_inputs(n, 1)
+    A32, B32 = A.astype(np.float32), B.astype(np.float32)
+    with pkg.GaussCuda(n, mode=pkg.MODE_3XTF32) as g:
+        X = g.gauss(A32, B32)
+        assert g.stats.zero_pivot_row == -1
+    resid = ol.scaled_residual(A32, B32, X)
+    nerr = ol.normwise_error(X, Xtrue)
+    print("n", n, "scaled residual", resid, "norm-wise error", nerr)
+    assert resid <= 10.0
+    assert nerr <= TOL
