@@ -472,7 +472,7 @@ def bench_gauss(args, pkg, D, workload, n, mode, peaks, peak_src, tf32, cores, s
         traffic, tnote = traffic_from_profile(workload, world, mode, nb_outer, pkg)
         roofline = {"bound": "tensor", "kernel": "tc_gemm_pair_kernel / tc_gemm_kernel (trailing update A22 -= L21*U12)" if mode == pkg.MODE_3XTF32 else "sgemm_nn_kernel",
                     "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic, "traffic_note": tnote,
-                    "peak_basis": basis, "launches": upd_launches, "avg_launch_ms": upd_s / max(upd_launches, 1) * 1e3,
+                    "peak_basis": basis, "peak_tf32_measured": tf32["tf32_tflops_sustained"] if tf32 else None, "launches": upd_launches, "avg_launch_ms": upd_s / max(upd_launches, 1) * 1e3,
                     "share_of_step": upd_s / max(fac_s + bs_s + rest_s, 1e-12),
                     "algorithmic_flops_per_step": upd_flop / steps}
         if mode == pkg.MODE_3XTF32:
