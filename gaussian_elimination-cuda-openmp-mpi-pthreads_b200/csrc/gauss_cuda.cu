@@ -190,6 +190,21 @@ struct gauss_cuda_ctx {
     std::vector<double> upd_flops;
     int upd_count = 0;
     ncclComm_t comm = nullptr;
+    // critical-path schedule (factor_cp): the diagonal region is factored in an extended scratch that also yields
+    // inv(L11) and inv(U11); both panel solves are GEMMs; the small "crit" package travels ahead of the bulk U12
+    bool cp = false;
+    float* ext = nullptr;                       // [2NB x 2NB] extended scratch E
+    float* ext_la[2] = {nullptr, nullptr};      // hi/lo [2NB x NB]  split L of the chain inside E
+    float* ext_ub[2] = {nullptr, nullptr};      // hi/lo [2NB x NB]  split U of the chain inside E (transposed)
+    float* il[2] = {nullptr, nullptr};          // hi/lo [NB x NB]   inv(L11), row-major
+    float* crit[2] = {nullptr, nullptr};        // per parity: iut_hi | iut_lo | uc_hi | uc_lo, NB x NB each (what the next panel needs first)
+    float* as_[2] = {nullptr, nullptr};         // hi/lo [rows_local x NB]  split of A21 before the solve (A operand of L21 = A21 inv(U11))
+    float* a12t[2] = {nullptr, nullptr};        // hi/lo [ld x NB]   split of A12 transposed (operand of both U12 GEMMs)
+    float* ut[2] = {nullptr, nullptr};          // per parity [ld x NB]  raw U12 transposed: the bulk broadcast payload
+    cudaEvent_t ev_crit[2] = {nullptr, nullptr}, ev_critlocal[2] = {nullptr, nullptr}, ev_critfree[2] = {nullptr, nullptr};
+    cudaEvent_t ev_ut[2] = {nullptr, nullptr}, ev_utlocal[2] = {nullptr, nullptr}, ev_utfree[2] = {nullptr, nullptr};
+    cudaEvent_t ev_la[2] = {nullptr, nullptr}, ev_colstrip[2] = {nullptr, nullptr}, ev_rowrest[2] = {nullptr, nullptr};
+    cudaEvent_t ev_inv[2] = {nullptr, nullptr}, ev_p4a = nullptr, ev_wjoin = nullptr;
     bool resident = false, factored = false;
     double bcast_bytes = 0.0;
     gauss_cuda_stats last{};
@@ -239,6 +254,12 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     { const char* e = getenv("GAUSS_CUDA_STREAM"); if (e && atoi(e) == 0) c->stream_on = false; }
     { const char* e = getenv("GAUSS_CUDA_STREAM_MIN_N"); if (e) c->stream_min_n = atoi(e); }
     { const char* e = getenv("GAUSS_CUDA_STREAM_CHUNKS"); if (e && atoi(e) > 0) c->stream_chunks = atoi(e); }
+    {   // schedule: the critical-path form is the multi-GPU default in 3xTF32 mode; GAUSS_CUDA_SCHED=cp selects it on one
+        // GPU too, GAUSS_CUDA_SCHED=lookahead keeps the round-1 multi-GPU pipeline (the FFMA mode always uses that one)
+        const char* e = getenv("GAUSS_CUDA_SCHED");
+        const bool want = e ? (strcmp(e, "cp") == 0) : (world > 1);
+        c->cp = want && mode == GAUSS_CUDA_MODE_3XTF32;
+    }
     c->np = round_up(n, kNb);
     c->ld = c->np + kPadCols;
     if (nb == 0) {
@@ -265,27 +286,44 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     A((void**)&c->trsv_ctrl, (size_t)(c->np / kNb + 1) * sizeof(int));
     A((void**)&c->sched, 128 * sizeof(int));
     if (e == cudaSuccess) e = cudaMemset(c->sched, 0, 128 * sizeof(int));
-    if (world > 1) for (int i = 0; i < 2; ++i) A((void**)&c->pbuf[i], (size_t)c->NB * c->ld * sizeof(float));
+    if (world > 1 && !c->cp) for (int i = 0; i < 2; ++i) A((void**)&c->pbuf[i], (size_t)c->NB * c->ld * sizeof(float));
+    if (c->cp) {
+        const size_t nb2 = (size_t)c->NB * c->NB * sizeof(float);
+        A((void**)&c->ext, 4 * nb2);
+        for (int i = 0; i < 2; ++i) {
+            A((void**)&c->ext_la[i], 2 * nb2); A((void**)&c->ext_ub[i], 2 * nb2);
+            A((void**)&c->il[i], nb2);
+            A((void**)&c->crit[i], 4 * nb2);
+            A((void**)&c->as_[i], (size_t)std::max(rows, 1) * c->NB * sizeof(float));
+            A((void**)&c->a12t[i], (size_t)c->ld * c->NB * sizeof(float));
+            A((void**)&c->ut[i], (size_t)c->ld * c->NB * sizeof(float));
+            if (e == cudaSuccess) e = cudaMemset(c->il[i], 0, nb2);
+            if (e == cudaSuccess) e = cudaMemset(c->crit[i], 0, 4 * nb2);
+            if (e == cudaSuccess) e = cudaMemset(c->a12t[i], 0, (size_t)c->ld * c->NB * sizeof(float));
+            if (e == cudaSuccess) e = cudaMemset(c->ut[i], 0, (size_t)c->ld * c->NB * sizeof(float));
+            if (e == cudaSuccess) e = cudaMemset(c->as_[i], 0, (size_t)std::max(rows, 1) * c->NB * sizeof(float));
+        }
+    }
     if (mode == GAUSS_CUDA_MODE_3XTF32) {
         const size_t la = (size_t)std::max(rows, 1) * c->NB * sizeof(float);
         const size_t ub = (size_t)c->ld * c->NB * sizeof(float);
         A((void**)&c->la_hi[0], la); A((void**)&c->la_lo[0], la);
-        if (c->overlap || world > 1) { A((void**)&c->la_hi[1], la); A((void**)&c->la_lo[1], la); }
-        for (int i = 0; i < ((world > 1 || c->overlap) ? 2 : 1); ++i) {
+        if (c->overlap || world > 1 || c->cp) { A((void**)&c->la_hi[1], la); A((void**)&c->la_lo[1], la); }
+        for (int i = 0; i < ((world > 1 || c->overlap || c->cp) ? 2 : 1); ++i) {
             A((void**)&c->ub_hi[i], ub); A((void**)&c->ub_lo[i], ub);
             if (e == cudaSuccess) e = cudaMemset(c->ub_hi[i], 0, ub);
             if (e == cudaSuccess) e = cudaMemset(c->ub_lo[i], 0, ub);
         }
     }
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking);
-    const bool dist_fork = world > 1 && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0);
+    const bool dist_fork = (world > 1 || c->cp) && !(getenv("GAUSS_CUDA_DIST_FORK") && atoi(getenv("GAUSS_CUDA_DIST_FORK")) == 0);
     if ((world == 1 && !(getenv("GAUSS_CUDA_INNER_FORK") && atoi(getenv("GAUSS_CUDA_INNER_FORK")) == 0)) || dist_fork) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_side, cudaStreamNonBlocking);
         if (c->wide_split) {
             int lo_p = 0, hi_p = 0;
             cudaDeviceGetStreamPriorityRange(&lo_p, &hi_p);
             // multi-GPU: the wide part of the panel factorisation belongs to the (priority) panel path
-            if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->s_wide, cudaStreamNonBlocking, world > 1 ? hi_p : lo_p);
+            if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&c->s_wide, cudaStreamNonBlocking, (world > 1 || c->cp) ? hi_p : lo_p);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_wide, cudaEventDisableTiming);
         }
         for (int i = 0; i < 8 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&c->ev_inner[i], cudaEventDisableTiming);
@@ -300,7 +338,14 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming);
         }
     }
-    if (world > 1) {
+    if (c->cp) {
+        cudaEvent_t* evs[] = {&c->ev_crit[0], &c->ev_crit[1], &c->ev_critlocal[0], &c->ev_critlocal[1], &c->ev_critfree[0], &c->ev_critfree[1],
+                              &c->ev_ut[0], &c->ev_ut[1], &c->ev_utlocal[0], &c->ev_utlocal[1], &c->ev_utfree[0], &c->ev_utfree[1],
+                              &c->ev_la[0], &c->ev_la[1], &c->ev_colstrip[0], &c->ev_colstrip[1], &c->ev_rowrest[0], &c->ev_rowrest[1],
+                              &c->ev_inv[0], &c->ev_inv[1], &c->ev_p4a, &c->ev_wjoin};
+        for (cudaEvent_t* ev : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+    }
+    if (world > 1 || c->cp) {
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->s_comm, cudaStreamNonBlocking);
         for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
             e = cudaEventCreateWithFlags(&c->ev_ready[i], cudaEventDisableTiming);
@@ -366,6 +411,16 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
     float* bufs[] = {c->W, c->W0, c->pbuf[0], c->pbuf[1], c->la_hi[0], c->la_lo[0], c->la_hi[1], c->la_lo[1],
                      c->ub_hi[0], c->ub_lo[0], c->ub_hi[1], c->ub_lo[1], c->xvec, c->hvec};
     for (float* b : bufs) if (b) cudaFree(b);
+    {
+        float* cpb[] = {c->ext, c->ext_la[0], c->ext_la[1], c->ext_ub[0], c->ext_ub[1], c->il[0], c->il[1], c->crit[0], c->crit[1],
+                        c->as_[0], c->as_[1], c->a12t[0], c->a12t[1], c->ut[0], c->ut[1]};
+        for (float* b : cpb) if (b) cudaFree(b);
+        cudaEvent_t evs[] = {c->ev_crit[0], c->ev_crit[1], c->ev_critlocal[0], c->ev_critlocal[1], c->ev_critfree[0], c->ev_critfree[1],
+                             c->ev_ut[0], c->ev_ut[1], c->ev_utlocal[0], c->ev_utlocal[1], c->ev_utfree[0], c->ev_utfree[1],
+                             c->ev_la[0], c->ev_la[1], c->ev_colstrip[0], c->ev_colstrip[1], c->ev_rowrest[0], c->ev_rowrest[1],
+                             c->ev_inv[0], c->ev_inv[1], c->ev_p4a, c->ev_wjoin};
+        for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
+    }
     if (c->status) cudaFree(c->status);
     if (c->gexec) cudaGraphExecDestroy(c->gexec);
     if (c->trsv_ctrl) cudaFree(c->trsv_ctrl);
@@ -961,6 +1016,237 @@ static int factor_lookahead(gauss_cuda_ctx* c)
     return GAUSS_CUDA_OK;
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Critical-path schedule.  The chain that bounds a multi-GPU factorisation is
+//     diagonal region of block K  ->  what block K+1's owner needs from it  ->  diagonal region of block K+1,
+// everything else (the wide U12, the bulk of the trailing update) has a whole step of slack.  This schedule keeps that
+// chain as short as the kernels allow:
+//   panel(K), owner     E = [[A11, I], [I, 0]] -> in-panel chain on E -> L11|U11, inv(L11), inv(U11)           (lu_cp.cu)
+//                       crit(K) = { inv(U11)^T split, U[K, K+1]^T split }  computed first and broadcast first
+//                       U12^T = A12^T inv(L11)^T as ONE GEMM into ut[] (broadcast second), U12 itself into the matrix
+//   every rank          L21 = A21 inv(U11) as ONE GEMM (+ split), the columns of block K+1 updated at once from crit(K)
+//                       (on the owner of K+1 that completes its next diagonal region), then the next A21 split;
+//                       ut[] split into the B operand when it arrives; bulk update on the main stream
+// The broadcasts are the reference's per-step MPI_Bcast of the pivot row (gauss_mpi/gauss_internal_input.c:137),
+// the row ownership its row blocks (:140-155).  world == 1 runs the same code without the collectives.
+// ------------------------------------------------------------------------------------------
+static int gemm_tc(gauss_cuda_ctx* c, cudaStream_t s, const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
+                   float* C, int ldc, int m, int n, int k, int sign, int beta, int max_tiles = 0)
+{
+    if (m <= 0 || n <= 0 || k <= 0) return GAUSS_CUDA_OK;
+    tc_set_sched_slots(c->sched);
+    tc_set_max_tiles(max_tiles);
+    tc_set_pair_ok(c->world == 1 || c->dist_pair);
+    int rc = tc_gemm_nt(Ahi, Alo, lda, Bhi, Blo, ldb, C, ldc, m, n, k, sign, beta, s);
+    tc_set_max_tiles(0);
+    tc_set_sched_slots(nullptr);
+    if (rc) return cuda_fail((cudaError_t)rc, "tc_gemm_nt", __LINE__);
+    return GAUSS_CUDA_OK;
+}
+
+// In-panel chain on the extended scratch: eliminates the first kb pivots of E (2kb x 2kb, leading dimension lde).
+static int ext_chain(gauss_cuda_ctx* c, int k0, int kb, cudaStream_t s)
+{
+    const int NB = c->NB, lde = 2 * NB, n2 = 2 * kb, ninner = kb / kNb;
+    float* E = c->ext;
+    for (int j = 0; j < ninner; ++j) {
+        const int r = j * kNb, rest = n2 - (r + kNb);
+        float* D = E + (size_t)r * lde + r;
+        launch_diag_factor(D, lde, k0 + r, c->status, s);
+        launch_urow_lcol(D, lde,
+                         D + kNb, lde, rest, c->ext_ub[0] + (size_t)(r + kNb) * NB, c->ext_ub[1] + (size_t)(r + kNb) * NB, NB, r,
+                         E + (size_t)(r + kNb) * lde + r, lde, rest, c->ext_la[0] + (size_t)(r + kNb) * NB, c->ext_la[1] + (size_t)(r + kNb) * NB, NB, r, s);
+        // rank-128 update of what is left of E; the last inner block only has the two identity strips left, whose
+        // product lands in the unused bottom-right block, so it is skipped
+        if (j + 1 < ninner) {
+            int rc = gemm_tc(c, s, c->ext_la[0] + (size_t)(r + kNb) * NB + r, c->ext_la[1] + (size_t)(r + kNb) * NB + r, NB,
+                             c->ext_ub[0] + (size_t)(r + kNb) * NB + r, c->ext_ub[1] + (size_t)(r + kNb) * NB + r, NB,
+                             E + (size_t)(r + kNb) * lde + r + kNb, lde, rest, rest, kNb, -1, 1);
+            if (rc) return rc;
+        }
+    }
+    return GAUSS_CUDA_OK;
+}
+
+static int factor_cp(gauss_cuda_ctx* c)
+{
+    cudaStream_t s = c->s_main, sc = c->s_comm, sp = c->s_panel, ss = c->s_side, sw = c->s_wide;
+    if (!sp || !ss || !sw || !sc) { snprintf(g_err, sizeof g_err, "critical-path schedule needs its side streams (GAUSS_CUDA_DIST_FORK/WIDE_SPLIT must stay on)"); return GAUSS_CUDA_BAD_ARG; }
+    const int ld = c->ld, NB = c->NB, nblk = c->nblk, lde = 2 * NB;
+    const size_t nb2 = (size_t)NB * NB;
+    auto owner_of = [&](int K) { return K % c->world; };
+    auto iut_hi = [&](int b) { return c->crit[b]; };
+    auto iut_lo = [&](int b) { return c->crit[b] + nb2; };
+    auto uc_hi = [&](int b) { return c->crit[b] + 2 * nb2; };
+    auto uc_lo = [&](int b) { return c->crit[b] + 3 * nb2; };
+    int rc;
+
+    // panel(K) on its owner, first half: diagonal region -> L11|U11, inv(L11) (il), inv(U11)^T (crit[b].iut)
+    auto panel_diag = [&](int K) -> int {
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
+        float* A11 = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+        CK(cudaStreamWaitEvent(sp, c->ev_critfree[b], 0));        // crit[b] (iut) of step K-2 has been consumed here
+        launch_ext_prepare(A11, ld, c->ext, lde, kb, sp);
+        if ((rc = ext_chain(c, k0, kb, sp))) return rc;
+        CK(cudaStreamWaitEvent(sp, c->ev_wjoin, 0));              // il is single-buffered: the previous row panel's GEMMs (one rank: ours) have read it
+        launch_ext_finish(c->ext, lde, kb, A11, ld, c->il[0], c->il[1], iut_hi(b), iut_lo(b), NB, sp);
+        CK(cudaEventRecord(c->ev_inv[b], sp));
+        return GAUSS_CUDA_OK;
+    };
+    // panel(K) on its owner, second half (the row panel right of the diagonal region must be final: ev_rowrest):
+    //   crit columns (those of block K+1) first on the panel stream, the rest on the wide stream
+    auto panel_row = [&](int K, bool have_rowrest) -> int {
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
+        const int c1 = k0 + kb;                                     // first column right of the diagonal region
+        const int ncols = ld - c1;
+        float* P = c->W + (size_t)blk_local_row(c, K) * ld;       // the row panel (kb rows)
+        const int ccrit = (K + 1 < nblk) ? blk_rows(c, K + 1) : 0;  // columns of block K+1
+        CK(cudaStreamWaitEvent(sp, c->ev_wjoin, 0));              // a12t is single-buffered too (previous row panel on the wide stream)
+        if (have_rowrest) {
+            CK(cudaStreamWaitEvent(sp, c->ev_rowrest[b ^ 1], 0));
+            CK(cudaStreamWaitEvent(sw, c->ev_rowrest[b ^ 1], 0));
+        }
+        if (ccrit > 0) {
+            CK(cudaStreamWaitEvent(sp, c->ev_utfree[b], 0));        // ut[b] of step K-2 has been split everywhere it is read here
+            launch_split_transpose(P + c1, ld, c->a12t[0] + (size_t)c1 * NB, c->a12t[1] + (size_t)c1 * NB, NB, kb, ccrit, kb, sp);
+            CK(cudaEventRecord(c->ev_p4a, sp));
+            // U[K, K+1]^T = A12^T inv(L11)^T  (kb_next x kb), raw into ut[b], then split into the crit package
+            if ((rc = gemm_tc(c, sp, c->a12t[0] + (size_t)c1 * NB, c->a12t[1] + (size_t)c1 * NB, NB, c->il[0], c->il[1], NB,
+                              c->ut[b] + (size_t)c1 * NB, NB, ccrit, kb, kb, +1, 0))) return rc;
+            launch_split_rowmajor(c->ut[b] + (size_t)c1 * NB, NB, uc_hi(b), uc_lo(b), NB, ccrit, kb, sp);
+            CK(cudaEventRecord(c->ev_critlocal[b], sp));
+        } else {
+            CK(cudaEventRecord(c->ev_p4a, sp));
+        }
+        // the rest of the row panel on the wide stream
+        CK(cudaStreamWaitEvent(sw, c->ev_inv[b], 0));
+        CK(cudaStreamWaitEvent(sw, c->ev_utfree[b], 0));
+        const int crest = c1 + ccrit, nrest = ld - crest;
+        if (nrest > 0) {
+            launch_split_transpose(P + crest, ld, c->a12t[0] + (size_t)crest * NB, c->a12t[1] + (size_t)crest * NB, NB, kb, nrest, kb, sw);
+            if (K + 1 < nblk) {
+                if ((rc = gemm_tc(c, sw, c->a12t[0] + (size_t)crest * NB, c->a12t[1] + (size_t)crest * NB, NB, c->il[0], c->il[1], NB,
+                                  c->ut[b] + (size_t)crest * NB, NB, nrest, kb, kb, +1, 0))) return rc;
+            }
+        }
+        CK(cudaStreamWaitEvent(sw, c->ev_critlocal[b], 0));         // (the crit rows of ut[b] are part of the bulk payload)
+        CK(cudaEventRecord(c->ev_utlocal[b], sw));
+        // U12 itself, in place, for back substitution (solveGauss reads the owner's rows): inv(L11) A12
+        CK(cudaStreamWaitEvent(sw, c->ev_p4a, 0));
+        if ((rc = gemm_tc(c, sw, c->il[0], c->il[1], NB, c->a12t[0] + (size_t)c1 * NB, c->a12t[1] + (size_t)c1 * NB, NB,
+                          P + c1, ld, kb, ncols, kb, +1, 0))) return rc;
+        CK(cudaEventRecord(c->ev_wjoin, sw));
+        return GAUSS_CUDA_OK;
+    };
+    // comm(K): crit package, then the bulk payload, from the owner to everyone (no-ops with one rank)
+    auto comm = [&](int K) -> int {
+        if (K + 1 >= nblk) return GAUSS_CUDA_OK;                   // the last block has nothing below or right of it
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K), c1 = k0 + kb;
+        const bool mine = owner_of(K) == c->rank;
+        if (mine) CK(cudaStreamWaitEvent(sc, c->ev_critlocal[b], 0));
+        else      CK(cudaStreamWaitEvent(sc, c->ev_critfree[b], 0));
+        if (c->world > 1) {
+            NK(g_nccl.Broadcast(c->crit[b], c->crit[b], 4 * nb2, ncclFloat, owner_of(K), c->comm, sc));
+            if (!mine) c->bcast_bytes += 4.0 * nb2 * sizeof(float);
+        }
+        CK(cudaEventRecord(c->ev_crit[b], sc));
+        if (mine) CK(cudaStreamWaitEvent(sc, c->ev_utlocal[b], 0));
+        else      CK(cudaStreamWaitEvent(sc, c->ev_utfree[b], 0));
+        if (c->world > 1) {
+            const size_t cnt = (size_t)(ld - c1) * NB;
+            NK(g_nccl.Broadcast(c->ut[b] + (size_t)c1 * NB, c->ut[b] + (size_t)c1 * NB, cnt, ncclFloat, owner_of(K), c->comm, sc));
+            if (!mine) c->bcast_bytes += (double)cnt * sizeof(float);
+        }
+        CK(cudaEventRecord(c->ev_ut[b], sc));
+        return GAUSS_CUDA_OK;
+    };
+
+    // ---- prologue
+    for (int i = 0; i < 2; ++i) {                                  // every double-buffered resource starts out free
+        CK(cudaEventRecord(c->ev_critfree[i], s));
+        CK(cudaEventRecord(c->ev_utfree[i], s));
+        CK(cudaEventRecord(c->ev_free[i], s));
+    }
+    CK(cudaEventRecord(c->ev_fork[0], s));                          // the side streams start after whatever precedes on the main stream
+    for (cudaStream_t st : {sp, ss, sw, sc}) CK(cudaStreamWaitEvent(st, c->ev_fork[0], 0));
+    {
+        const int l0 = first_local_block_after(c, 0) * NB, m = c->rows_local - l0;
+        if (m > 0 && nblk > 1)
+            launch_split_rowmajor(c->W + (size_t)l0 * ld, ld, c->as_[0] + (size_t)l0 * NB, c->as_[1] + (size_t)l0 * NB, NB, m, blk_rows(c, 0), ss);
+    }
+    if (owner_of(0) == c->rank) {
+        if ((rc = panel_diag(0))) return rc;
+        if ((rc = panel_row(0, false))) return rc;
+    }
+    if ((rc = comm(0))) return rc;
+
+    // ---- steps
+    for (int K = 0; K + 1 < nblk; ++K) {
+        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
+        const int rows_next = blk_rows(c, K + 1), cnext = k0 + kb;
+        const bool own_next = owner_of(K + 1) == c->rank;
+        const int l0 = first_local_block_after(c, K) * NB;          // first local row below block K
+        const int m = c->rows_local - l0;
+        const int l1 = own_next ? l0 + rows_next : l0;              // first local row below block K+1
+        float* Wb = c->W + (size_t)l0 * ld;
+
+        // 1. side stream: L21 = A21 inv(U11) (+ split), columns of block K+1, next A21 split
+        CK(cudaStreamWaitEvent(ss, c->ev_crit[b], 0));
+        CK(cudaStreamWaitEvent(ss, c->ev_free[b], 0));              // la[b] of step K-2 no longer read by its bulk update
+        if (m > 0) {
+            if ((rc = gemm_tc(c, ss, c->as_[0] + (size_t)l0 * NB, c->as_[1] + (size_t)l0 * NB, NB, iut_hi(b), iut_lo(b), NB,
+                              Wb + k0, ld, m, kb, kb, +1, 0))) return rc;
+            launch_split_rowmajor(Wb + k0, ld, c->la_hi[b] + (size_t)l0 * NB, c->la_lo[b] + (size_t)l0 * NB, NB, m, kb, ss);
+        }
+        CK(cudaEventRecord(c->ev_la[b], ss));
+        // block column K+1 has received panel K-1's contribution through the bulk update of step K-1: that must be complete
+        // before this step's contribution is added and the column is read (next A21 split, next diagonal region)
+        CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
+        if (m > 0) {
+            if ((rc = gemm_tc(c, ss, c->la_hi[b] + (size_t)l0 * NB, c->la_lo[b] + (size_t)l0 * NB, NB, uc_hi(b), uc_lo(b), NB,
+                              Wb + cnext, ld, m, rows_next, kb, -1, 1))) return rc;
+        }
+        CK(cudaEventRecord(c->ev_colstrip[b], ss));
+        CK(cudaEventRecord(c->ev_critfree[b], ss));
+        if (c->rows_local - l1 > 0 && K + 2 < nblk)
+            launch_split_rowmajor(c->W + (size_t)l1 * ld + cnext, ld, c->as_[0] + (size_t)l1 * NB, c->as_[1] + (size_t)l1 * NB, NB,
+                                  c->rows_local - l1, rows_next, ss);
+
+        // 2. panel stream (owner of K+1): its diagonal region is final after the column strip
+        if (own_next) {
+            CK(cudaStreamWaitEvent(sp, c->ev_colstrip[b], 0));
+            if ((rc = panel_diag(K + 1))) return rc;
+        }
+
+        // 3. main stream: U12^T of step K arrives -> B operand; the rest of block K+1's rows
+        CK(cudaStreamWaitEvent(s, c->ev_ut[b], 0));
+        launch_split_rowmajor(c->ut[b] + (size_t)cnext * NB, NB, c->ub_hi[b] + (size_t)cnext * NB, c->ub_lo[b] + (size_t)cnext * NB, NB,
+                              ld - cnext, kb, s);
+        CK(cudaEventRecord(c->ev_utfree[b], s));
+        CK(cudaStreamWaitEvent(s, c->ev_la[b], 0));
+        const PanelRef pr{nullptr, 0, nullptr, 0, c->ub_hi[b], c->ub_lo[b]};
+        const StepBufs sbm{s, c->la_hi[b], c->la_lo[b]};
+        if (own_next) {
+            if ((rc = trailing_update(c, K, pr, sbm, l0, l1, cnext + rows_next, -1))) return rc;
+            CK(cudaEventRecord(c->ev_rowrest[b], s));
+            // 4. the row panel of block K+1: crit package first, wide part beside it
+            if ((rc = panel_row(K + 1, true))) return rc;
+        }
+        // 5. communication of step K+1
+        if ((rc = comm(K + 1))) return rc;
+        // 6. bulk of the trailing update (CTAs give up their SM every few tiles: the other streams have priority)
+        if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1, c->overlap_max_tiles))) return rc;
+        CK(cudaEventRecord(c->ev_free[b], s));
+    }
+    // ---- join everything back into the main stream
+    CK(cudaEventRecord(c->ev_join[0], sp)); CK(cudaStreamWaitEvent(s, c->ev_join[0], 0));
+    CK(cudaEventRecord(c->ev_join[1], ss)); CK(cudaStreamWaitEvent(s, c->ev_join[1], 0));
+    CK(cudaEventRecord(c->ev_wjoin, sw));   CK(cudaStreamWaitEvent(s, c->ev_wjoin, 0));
+    CK(cudaEventRecord(c->ev_done[0], sc)); CK(cudaStreamWaitEvent(s, c->ev_done[0], 0));
+    return GAUSS_CUDA_OK;
+}
+
 // Partial pivoting (gauss_external_input.c:123-182): single-level blocking, one 128-column panel at a
 // time -- pivoted panel factorisation over all rows below, interchanges applied to the right-hand part,
 // U-row solve, rank-128 trailing update (the no-pivot kernels from there on).
@@ -995,6 +1281,7 @@ static int factor(gauss_cuda_ctx* c)
     c->bcast_bytes = 0.0;
     c->upd_count = 0;
     int rc = c->pivot ? factor_pivot(c)
+           : c->cp ? factor_cp(c)
            : c->world > 1 ? factor_lookahead(c)
            : (c->overlap && c->nblk >= 3) ? factor_overlap(c) : factor_single(c);
     if (rc) return rc;
@@ -1129,7 +1416,7 @@ static int core_body(gauss_cuda_ctx* c)
 static int run_core(gauss_cuda_ctx* c)
 {
     cudaStream_t s = c->s_main;
-    const bool graphable = c->world == 1 && !c->pivot && c->use_graph && !c->graph_failed;
+    const bool graphable = c->world == 1 && !c->pivot && !c->cp && c->use_graph && !c->graph_failed;
     if (graphable && !c->gexec) {
         const long long before = g_launch_count;
         c->capturing = true;
@@ -1189,7 +1476,7 @@ extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* 
     g_launch_count = 0;
     cudaStream_t s = c->s_main;
     int rc;
-    c->last_streamed = c->world == 1 && !c->pivot && c->stream_on && c->np >= c->stream_min_n && c->nblk >= 2;
+    c->last_streamed = c->world == 1 && !c->pivot && !c->cp && c->stream_on && c->np >= c->stream_min_n && c->nblk >= 2;
     if (c->last_streamed && (rc = stream_setup(c))) return rc;
     CK(cudaEventRecord(c->ev[0], s));
     if (c->last_streamed) {

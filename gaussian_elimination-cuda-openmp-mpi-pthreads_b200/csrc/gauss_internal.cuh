@@ -67,6 +67,13 @@ void panel_setup_device();    // same for lu_panel.cu (called by simt_setup_devi
 int  tc_setup_device(bool reread_env = true);   // same for the tile engine; returns a GAUSS_CUDA_* status.  reread_env = false leaves the
                                                 // process-wide GAUSS_CUDA_TC_* switches alone once some caller has read them
 
+// ---- critical-path schedule helpers (lu_cp.cu) ------------------------------------------------
+// E[0:2kb, 0:2kb] <- [[A11, I], [I, 0]]; after the in-panel chain on E: [[L11|U11, inv(L11)], [inv(U11), *]].
+void launch_ext_prepare(const float* a11, int ld, float* E, int lde, int kb, cudaStream_t s);
+// L11|U11 back into the matrix; il_* = hi/lo split of inv(L11) (row-major, ldo); iut_* = hi/lo split of inv(U11)^T.
+void launch_ext_finish(const float* E, int lde, int kb, float* a11, int ld,
+                       float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo, cudaStream_t s);
+
 // ---- partial-pivoting panel (lu_pivot.cu) --------------------------------------------------
 // Factors the panel W[k0.., k0..k0+128) of an [np x ld] single-GPU system with row interchanges
 // (gauss_external_input.c:123-148, 161-181); see lu_pivot.cu.  la_* (may be null): split of the rows
