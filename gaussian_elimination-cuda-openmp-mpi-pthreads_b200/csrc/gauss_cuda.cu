@@ -358,9 +358,9 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         }
     }
     for (int i = 0; i < 6 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
-    c->trace = world > 1 && getenv("GAUSS_CUDA_TRACE") && atoi(getenv("GAUSS_CUDA_TRACE")) != 0;
+    c->trace = (world > 1 || c->cp) && getenv("GAUSS_CUDA_TRACE") && atoi(getenv("GAUSS_CUDA_TRACE")) != 0;
     if (c->trace) {
-        c->tr_ev.assign(6 * (size_t)c->nblk, nullptr);
+        c->tr_ev.assign(8 * (size_t)c->nblk, nullptr);
         for (size_t i = 0; i < c->tr_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->tr_ev[i]);
     }
     c->upd_ev.assign(6 * (size_t)c->nblk, nullptr);            // look-ahead splits the update in up to three launches
@@ -962,7 +962,7 @@ static int factor_lookahead(gauss_cuda_ctx* c)
         const bool mine = owner_of(K) == c->rank;
         const PanelRef pr = panel_ref(K);
         const StepBufs sbm{s, c->la_hi[b], c->la_lo[b]};
-        auto mark = [&](int i) { if (c->trace) cudaEventRecord(c->tr_ev[6 * (size_t)K + i], s); };
+        auto mark = [&](int i) { if (c->trace) cudaEventRecord(c->tr_ev[8 * (size_t)K + i], s); };
         mark(0);                                                  // step begins (previous bulk + P2 join done)
         if (!mine) {
             CK(cudaStreamWaitEvent(s, c->ev_done[b], 0));         // the U12 region has arrived
@@ -1116,6 +1116,7 @@ static int factor_cp(gauss_cuda_ctx* c)
                               c->ut[b] + (size_t)c1 * NB, NB, ccrit, kb, kb, +1, 0))) return rc;
             launch_split_rowmajor(c->ut[b] + (size_t)c1 * NB, NB, uc_hi(b), uc_lo(b), NB, ccrit, kb, sp);
             CK(cudaEventRecord(c->ev_critlocal[b], sp));
+            if (c->trace && K > 0) cudaEventRecord(c->tr_ev[8 * (size_t)(K - 1) + 4], sp);
         } else {
             CK(cudaEventRecord(c->ev_p4a, sp));
         }
@@ -1191,15 +1192,18 @@ static int factor_cp(gauss_cuda_ctx* c)
         const int l1 = own_next ? l0 + rows_next : l0;              // first local row below block K+1
         float* Wb = c->W + (size_t)l0 * ld;
 
+        auto mark = [&](int i, cudaStream_t st) { if (c->trace) cudaEventRecord(c->tr_ev[8 * (size_t)K + i], st); };
         // 1. side stream: L21 = A21 inv(U11) (+ split), columns of block K+1, next A21 split
         CK(cudaStreamWaitEvent(ss, c->ev_crit[b], 0));
         CK(cudaStreamWaitEvent(ss, c->ev_free[b], 0));              // la[b] of step K-2 no longer read by its bulk update
+        mark(0, ss);
         if (m > 0) {
             if ((rc = gemm_tc(c, ss, c->as_[0] + (size_t)l0 * NB, c->as_[1] + (size_t)l0 * NB, NB, iut_hi(b), iut_lo(b), NB,
                               Wb + k0, ld, m, kb, kb, +1, 0))) return rc;
             launch_split_rowmajor(Wb + k0, ld, c->la_hi[b] + (size_t)l0 * NB, c->la_lo[b] + (size_t)l0 * NB, NB, m, kb, ss);
         }
         CK(cudaEventRecord(c->ev_la[b], ss));
+        mark(1, ss);
         // block column K+1 has received panel K-1's contribution through the bulk update of step K-1: that must be complete
         // before this step's contribution is added and the column is read (next A21 split, next diagonal region)
         CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
@@ -1209,6 +1213,7 @@ static int factor_cp(gauss_cuda_ctx* c)
         }
         CK(cudaEventRecord(c->ev_colstrip[b], ss));
         CK(cudaEventRecord(c->ev_critfree[b], ss));
+        mark(2, ss);
         if (c->rows_local - l1 > 0 && K + 2 < nblk)
             launch_split_rowmajor(c->W + (size_t)l1 * ld + cnext, ld, c->as_[0] + (size_t)l1 * NB, c->as_[1] + (size_t)l1 * NB, NB,
                                   c->rows_local - l1, rows_next, ss);
@@ -1217,10 +1222,12 @@ static int factor_cp(gauss_cuda_ctx* c)
         if (own_next) {
             CK(cudaStreamWaitEvent(sp, c->ev_colstrip[b], 0));
             if ((rc = panel_diag(K + 1))) return rc;
+            mark(3, sp);
         }
 
         // 3. main stream: U12^T of step K arrives -> B operand; the rest of block K+1's rows
         CK(cudaStreamWaitEvent(s, c->ev_ut[b], 0));
+        mark(6, s);
         launch_split_rowmajor(c->ut[b] + (size_t)cnext * NB, NB, c->ub_hi[b] + (size_t)cnext * NB, c->ub_lo[b] + (size_t)cnext * NB, NB,
                               ld - cnext, kb, s);
         CK(cudaEventRecord(c->ev_utfree[b], s));
@@ -1233,11 +1240,13 @@ static int factor_cp(gauss_cuda_ctx* c)
             // 4. the row panel of block K+1: crit package first, wide part beside it
             if ((rc = panel_row(K + 1, true))) return rc;
         }
+        mark(7, s);
         // 5. communication of step K+1
         if ((rc = comm(K + 1))) return rc;
         // 6. bulk of the trailing update (CTAs give up their SM every few tiles: the other streams have priority)
         if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1, c->overlap_max_tiles))) return rc;
         CK(cudaEventRecord(c->ev_free[b], s));
+        mark(5, s);
     }
     // ---- join everything back into the main stream
     CK(cudaEventRecord(c->ev_join[0], sp)); CK(cudaStreamWaitEvent(s, c->ev_join[0], 0));
@@ -1349,14 +1358,38 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
             }
         }
     }
-    if (c->trace && fac) {
+    if (c->trace && fac && c->cp) {
+        // critical-path schedule, per rank: side stream [0 crit arrived -> 1 L21 GEMM + split -> 2 column strip], panel stream
+        // (owner of K+1) [2 -> 3 diagonal region chain -> 4 crit columns of U12], main stream [6 U12^T arrived -> 7 split +
+        // row strip -> 5 bulk done]; with one rank [4 of step K -> 0 of step K+1] is the hand-over
+        double a_p2 = 0, a_cs = 0, a_chain = 0, a_cu = 0, a_hand = 0, a_utwait = 0, a_split = 0, a_bulk = 0, a_crit2crit = 0;
+        int n_chain = 0;
+        auto el2 = [&](int Ka, int ia, int Kb, int ib, double& acc) -> bool {
+            if (Ka < 0 || Kb < 0 || Ka >= c->nblk || Kb >= c->nblk) return false;
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, c->tr_ev[8 * (size_t)Ka + ia], c->tr_ev[8 * (size_t)Kb + ib]) != cudaSuccess) { cudaGetLastError(); return false; }
+            acc += ms; return true;
+        };
+        for (int K = 0; K + 1 < c->nblk; ++K) {
+            el2(K, 0, K, 1, a_p2); el2(K, 1, K, 2, a_cs);
+            if (K % c->world == (c->rank + c->world - 1) % c->world && el2(K, 2, K, 3, a_chain)) ++n_chain;
+            if (K % c->world == (c->rank + c->world - 1) % c->world) el2(K, 3, K, 4, a_cu);
+            if (c->world == 1) el2(K, 4, K + 1, 0, a_hand);
+            el2(K, 0, K + 1, 0, a_crit2crit);
+            el2(K - 1, 5, K, 6, a_utwait); el2(K, 6, K, 7, a_split); el2(K, 7, K, 5, a_bulk);
+        }
+        cudaGetLastError();
+        fprintf(stderr, "[gauss_cuda trace cp] rank %d/%d nb %d: side L21 %.2f ms, col strip %.2f | panel chain %.2f (%d panels), crit U %.2f, hand-over %.2f | "
+                        "crit-to-crit %.2f | main: wait U12 %.2f, split+row strip %.2f, bulk %.2f (factor %.2f ms)\n",
+                c->rank, c->world, c->NB, a_p2, a_cs, a_chain, n_chain, a_cu, a_hand, a_crit2crit, a_utwait, a_split, a_bulk, o.factor_s * 1e3);
+    } else if (c->trace && fac) {
         // where the main stream's time went: [0->1] waiting for the U12 broadcast, [1->2] rebuilding the split,
         // [2->3] row strip, [3->4] column strip, [4->5] bulk update, [5->next 0] waiting for P2 of the next panel
         double acc[6] = {0, 0, 0, 0, 0, 0};
         for (int K = 0; K + 1 < c->nblk; ++K) {
             for (int i = 0; i < 6; ++i) {
-                cudaEvent_t a = c->tr_ev[6 * (size_t)K + i];
-                cudaEvent_t b2 = i < 5 ? c->tr_ev[6 * (size_t)K + i + 1] : c->tr_ev[6 * (size_t)(K + 1)];
+                cudaEvent_t a = c->tr_ev[8 * (size_t)K + i];
+                cudaEvent_t b2 = i < 5 ? c->tr_ev[8 * (size_t)K + i + 1] : c->tr_ev[8 * (size_t)(K + 1)];
                 float ms = 0.f;
                 if (cudaEventElapsedTime(&ms, a, b2) == cudaSuccess) acc[i] += ms;
             }
