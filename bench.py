@@ -543,6 +543,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the gauss2048 / matmul2048 block of the default run")
     ap.add_argument("--no-tf32-probe", action="store_true")
+    ap.add_argument("--env-sweep", default="", help="tuning aid: KEY=v1,v2,... runs the workload once per value of the library's environment switch KEY "
+                                                   "(read when the context is created) and prints the list under 'sweep'")
+    ap.add_argument("--no-parity-exit", action="store_true", help="tuning aid: report parity but do not exit 3 (timing diagnostics that skip work)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
 
@@ -582,6 +585,21 @@ def main():
         return
 
     small = n <= 8192                       # fits in L2 many times over: flush between iterations, CPU baseline at the same N
+    if args.env_sweep:
+        key, vals = args.env_sweep.split("=", 1)
+        out = []
+        for v in vals.split(","):
+            os.environ[key] = v
+            l, ok = bench_gauss(args, pkg, D, args.workload, n, mode, peaks, peak_src, tf32, cores, args.steps, args.warmup,
+                                with_e2e=False, with_cpu=False, flush_l2=small)
+            if rank == 0:
+                out.append({"env": f"{key}={v}", "value": l["value"], "ms_per_step": l["ms_per_step"], "breakdown_ms": l["breakdown_ms"],
+                            "parity": {k: l["parity"][k] for k in ("max_rel_err", "scaled_residual", "ok")},
+                            "update_tflops_per_launch": l["roofline"]["achieved"] if l["roofline"] else None})
+        if rank == 0:
+            emit({"metric": METRIC, "unit": UNIT, "n_gpus": D.world, "config": {"workload": args.workload, "n": n, "nb": args.nb}, "sweep": out})
+        D.close()
+        return
     line, ok = bench_gauss(args, pkg, D, args.workload, n, mode, peaks, peak_src, tf32, cores, args.steps, args.warmup,
                            with_e2e=not args.no_e2e, with_cpu=not args.no_cpu_baseline, flush_l2=small, cpu_same_n=small)
     if rank == 0 and tf32:
@@ -602,7 +620,7 @@ def main():
     if rank == 0:
         emit(line)
     D.close()
-    if not ok:
+    if not ok and not args.no_parity_exit:
         sys.stderr.write("bench.py: PARITY FAILED (see the line's parity block)\n")
         sys.exit(3)
 

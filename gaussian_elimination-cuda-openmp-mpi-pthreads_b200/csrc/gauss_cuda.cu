@@ -77,6 +77,7 @@ struct NcclApi {
     ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
@@ -92,6 +93,7 @@ static int nccl_load()
     g_nccl.GetUniqueId    = (decltype(g_nccl.GetUniqueId))dlsym(h, "ncclGetUniqueId");
     g_nccl.CommInitRank   = (decltype(g_nccl.CommInitRank))dlsym(h, "ncclCommInitRank");
     g_nccl.Broadcast      = (decltype(g_nccl.Broadcast))dlsym(h, "ncclBroadcast");
+    g_nccl.AllGather      = (decltype(g_nccl.AllGather))dlsym(h, "ncclAllGather");
     g_nccl.CommDestroy    = (decltype(g_nccl.CommDestroy))dlsym(h, "ncclCommDestroy");
     g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(h, "ncclGetErrorString");
     if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.Broadcast || !g_nccl.CommDestroy) {
@@ -193,6 +195,15 @@ struct gauss_cuda_ctx {
     // critical-path schedule (factor_cp): the diagonal region is factored in an extended scratch that also yields
     // inv(L11) and inv(U11); both panel solves are GEMMs; the small "crit" package travels ahead of the bulk U12
     bool cp = false;
+    int cp_reserve = 16;                        // SMs the bulk update leaves to the panel chain (GAUSS_CUDA_CP_RESERVE)
+    // peer-memory push of the crit package to the next owner (multi-GPU, one process per GPU: CUDA IPC mapping)
+    bool p2p = false;
+    float* pbox = nullptr;                      // this rank's receive box: [1024 B of flag words | pcrit[0] | pcrit[1]], pcrit = 4 x NB x NB floats
+    float* peer_pbox = nullptr;                 // the next rank's box, mapped into this process
+    unsigned* push_counters = nullptr;          // device: completion counters of the two pushing kernels
+    unsigned solve_seq = 0;                     // factorisations run by this context (every rank counts alike): flag values are seq * nblk + K + 1
+    bool memops = false;                        // cuStreamWaitValue32 available (else a spinning one-warp kernel waits)
+    bool cp_nobulk = false;                     // GAUSS_CUDA_CP_NOBULK=1: timing diagnostic only (WRONG results): the bulk update is skipped
     float* ext = nullptr;                       // [2NB x 2NB] extended scratch E
     float* ext_la[2] = {nullptr, nullptr};      // hi/lo [2NB x NB]  split L of the chain inside E
     float* ext_ub[2] = {nullptr, nullptr};      // hi/lo [2NB x NB]  split U of the chain inside E (transposed)
@@ -221,6 +232,64 @@ static inline int first_local_block_after(const gauss_cuda_ctx* c, int K) { retu
 // number of local blocks whose global block index is < K   (rows strictly above outer block K)
 static inline int local_blocks_before(const gauss_cuda_ctx* c, int K) { return K > c->rank ? (K - c->rank - 1) / c->world + 1 : 0; }
 
+
+// Stream memory operations (cuStreamWaitValue32), fetched through the runtime like the tensor-map encoder
+typedef int (*StreamWaitValue32Fn)(cudaStream_t, unsigned long long, unsigned, unsigned);
+static StreamWaitValue32Fn g_wait_value32 = nullptr;
+
+// Maps the NEXT rank's receive box into this process (CUDA IPC) so the kernels that produce the crit package can store
+// it there directly.  Collective over the context's communicator; when any rank cannot map its neighbour (no peer
+// access, GAUSS_CUDA_P2P=0) every rank falls back to the broadcast alone.
+static int p2p_setup(gauss_cuda_ctx* c)
+{
+    const size_t nb2 = (size_t)c->NB * c->NB;
+    const size_t box_bytes = 1024 + 8 * nb2 * sizeof(float);
+    CK(cudaMalloc((void**)&c->pbox, box_bytes));
+    CK(cudaMemset(c->pbox, 0, box_bytes));
+    CK(cudaMalloc((void**)&c->push_counters, 64));
+    CK(cudaMemset(c->push_counters, 0, 64));
+    if (!g_nccl.AllGather) return GAUSS_CUDA_OK;                   // old NCCL without the symbol: broadcast only
+    unsigned char* stage = nullptr;
+    const size_t slot = 128;
+    CK(cudaMalloc((void**)&stage, slot * (c->world + 1)));
+    std::vector<unsigned char> host(slot * (c->world + 1), 0);
+    cudaIpcMemHandle_t h;
+    int ok = cudaIpcGetMemHandle(&h, c->pbox) == cudaSuccess ? 1 : 0;
+    cudaGetLastError();
+    memcpy(host.data(), &h, sizeof h);
+    CK(cudaMemcpy(stage, host.data(), slot, cudaMemcpyHostToDevice));
+    NK(g_nccl.AllGather(stage, stage + slot, slot, ncclChar, c->comm, c->s_main));
+    CK(cudaStreamSynchronize(c->s_main));
+    CK(cudaMemcpy(host.data(), stage, slot * (c->world + 1), cudaMemcpyDeviceToHost));
+    const char* env = getenv("GAUSS_CUDA_P2P");
+    if (env && atoi(env) == 0) ok = 0;
+    if (ok) {
+        cudaIpcMemHandle_t hn;
+        memcpy(&hn, host.data() + slot * (1 + (c->rank + 1) % c->world), sizeof hn);
+        void* p = nullptr;
+        if (cudaIpcOpenMemHandle(&p, hn, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess) c->peer_pbox = (float*)p;
+        else { ok = 0; cudaGetLastError(); }
+    }
+    memset(host.data(), 0, slot);
+    host[0] = (unsigned char)ok;
+    CK(cudaMemcpy(stage, host.data(), slot, cudaMemcpyHostToDevice));
+    NK(g_nccl.AllGather(stage, stage + slot, slot, ncclChar, c->comm, c->s_main));
+    CK(cudaStreamSynchronize(c->s_main));
+    CK(cudaMemcpy(host.data(), stage, slot * (c->world + 1), cudaMemcpyDeviceToHost));
+    bool all = true;
+    for (int r = 0; r < c->world; ++r) all = all && host[slot * (1 + r)] == 1;
+    CK(cudaFree(stage));
+    c->p2p = all;
+    if (!g_wait_value32) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &q) == cudaSuccess && fn) g_wait_value32 = (StreamWaitValue32Fn)fn;
+        cudaGetLastError();
+    }
+    const char* mo = getenv("GAUSS_CUDA_MEMOPS");
+    c->memops = g_wait_value32 != nullptr && !(mo && atoi(mo) == 0);
+    return GAUSS_CUDA_OK;
+}
 
 static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int device, const void* nccl_id, int nb, int mode)
 {
@@ -259,6 +328,10 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         const char* e = getenv("GAUSS_CUDA_SCHED");
         const bool want = e ? (strcmp(e, "cp") == 0) : (world > 1);
         c->cp = want && mode == GAUSS_CUDA_MODE_3XTF32;
+        const char* r = getenv("GAUSS_CUDA_CP_RESERVE");
+        if (r) c->cp_reserve = std::max(0, std::min(64, atoi(r)));
+        const char* nbk = getenv("GAUSS_CUDA_CP_NOBULK");
+        c->cp_nobulk = nbk && atoi(nbk) != 0;
     }
     c->np = round_up(n, kNb);
     c->ld = c->np + kPadCols;
@@ -375,6 +448,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         memcpy(&id, nccl_id, sizeof id);
         ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
         if (r != ncclSuccess) { rc = nccl_fail(r, "ncclCommInitRank", __LINE__); gauss_cuda_free(c); return rc; }
+        if (c->cp && (rc = p2p_setup(c))) { gauss_cuda_free(c); return rc; }
     }
     *out = c;
     return GAUSS_CUDA_OK;
@@ -421,6 +495,9 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
                              c->ev_inv[0], c->ev_inv[1], c->ev_p4a, c->ev_wjoin};
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
     }
+    if (c->peer_pbox) cudaIpcCloseMemHandle(c->peer_pbox);
+    if (c->pbox) cudaFree(c->pbox);
+    if (c->push_counters) cudaFree(c->push_counters);
     if (c->status) cudaFree(c->status);
     if (c->gexec) cudaGraphExecDestroy(c->gexec);
     if (c->trsv_ctrl) cudaFree(c->trsv_ctrl);
@@ -500,7 +577,7 @@ static int upload_into(gauss_cuda_ctx* c, float* dst, const float* A, const floa
 // ------------------------------------------------------------------------------------------
 static int gemm_update(gauss_cuda_ctx* c, cudaStream_t s, const float* A, int lda, const float* B, int ldb,
                        const float* Ahi, const float* Alo, const float* Bhi, const float* Blo,
-                       float* C, int m, int ncols, int k, int max_tiles = 0)
+                       float* C, int m, int ncols, int k, int max_tiles = 0, int reserve = 0)
 {
     if (m <= 0 || ncols <= 0) return GAUSS_CUDA_OK;
     if (c->mode == GAUSS_CUDA_MODE_FFMA) {
@@ -510,7 +587,9 @@ static int gemm_update(gauss_cuda_ctx* c, cudaStream_t s, const float* A, int ld
     tc_set_sched_slots(c->sched);
     tc_set_max_tiles(max_tiles);
     tc_set_pair_ok(c->world == 1 || c->dist_pair);
+    tc_set_reserve_sms(reserve);
     int rc = tc_gemm_nt(Ahi, Alo, c->NB, Bhi, Blo, c->NB, C, c->ld, m, ncols, k, -1, 1, s);
+    tc_set_reserve_sms(0);
     tc_set_max_tiles(0);
     tc_set_sched_slots(nullptr);
     if (rc) return cuda_fail((cudaError_t)rc, "tc_gemm_nt", __LINE__);
@@ -641,7 +720,7 @@ static int col_panel(gauss_cuda_ctx* c, int K, const PanelRef& pr, int row_lo, c
 // panel (ncols < 0: all of them).  Timed.  max_tiles > 0 bounds how many tiles a CTA of the tile engine takes
 // before it exits, so that kernels of the (higher-priority) panel stream get SMs while this launch runs.
 static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const StepBufs& sb, int row_lo, int row_hi,
-                           int col_lo = -1, int ncols = -1, int max_tiles = 0)
+                           int col_lo = -1, int ncols = -1, int max_tiles = 0, int reserve = 0)
 {
     cudaStream_t s = sb.s;
     const int ld = c->ld, NB = c->NB, np = c->np;
@@ -658,7 +737,7 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const S
     int rc = gemm_update(c, s, Wb + k0, ld, pr.pu + (col_lo - (k0 + kb)), pr.ldu,
                          tc ? sb.la_hi + (size_t)row_lo * NB : nullptr, tc ? sb.la_lo + (size_t)row_lo * NB : nullptr,
                          tc ? pr.ub_hi + (size_t)col_lo * NB : nullptr, tc ? pr.ub_lo + (size_t)col_lo * NB : nullptr,
-                         Wb + col_lo, m, ncols, kb, max_tiles);
+                         Wb + col_lo, m, ncols, kb, max_tiles, reserve);
     if (rc) return rc;
     if (timed) {
         CK(rec_event(c, c->upd_ev[2 * ui + 1], s));
@@ -1081,6 +1160,22 @@ static int factor_cp(gauss_cuda_ctx* c)
     auto uc_hi = [&](int b) { return c->crit[b] + 2 * nb2; };
     auto uc_lo = [&](int b) { return c->crit[b] + 3 * nb2; };
     int rc;
+    // peer push: the owner of K stores crit(K) into the box of the owner of K+1 (always the next rank); the receiver
+    // double-buffers by the parity of its own use count ((K+1) / world) and waits for flag words 0 (inv(U11)^T) and 32 (U^T)
+    c->solve_seq += 1;
+    const bool p2p = c->p2p && c->world > 1;
+    auto pq = [&](int K) { return ((K + 1) / c->world) & 1; };
+    auto seq_of = [&](int K) { return (unsigned)(c->solve_seq * (unsigned)nblk + (unsigned)K + 1u); };
+    auto box_crit = [&](float* box, int q) { return box + 256 + (size_t)q * 4 * nb2; };
+    auto wait_flag = [&](cudaStream_t st, int word, unsigned value) -> int {
+        const unsigned* f = reinterpret_cast<const unsigned*>(c->pbox) + word;
+        if (c->memops) {
+            if (g_wait_value32(st, (unsigned long long)(uintptr_t)f, value, 0x0 /* CU_STREAM_WAIT_VALUE_GEQ */) != 0) {
+                snprintf(g_err, sizeof g_err, "cuStreamWaitValue32 failed"); return GAUSS_CUDA_CUDA_ERR;
+            }
+        } else launch_wait_flag(f, value, st);
+        return GAUSS_CUDA_OK;
+    };
 
     // panel(K) on its owner, first half: diagonal region -> L11|U11, inv(L11) (il), inv(U11)^T (crit[b].iut)
     auto panel_diag = [&](int K) -> int {
@@ -1090,7 +1185,10 @@ static int factor_cp(gauss_cuda_ctx* c)
         launch_ext_prepare(A11, ld, c->ext, lde, kb, sp);
         if ((rc = ext_chain(c, k0, kb, sp))) return rc;
         CK(cudaStreamWaitEvent(sp, c->ev_wjoin, 0));              // il is single-buffered: the previous row panel's GEMMs (one rank: ours) have read it
-        launch_ext_finish(c->ext, lde, kb, A11, ld, c->il[0], c->il[1], iut_hi(b), iut_lo(b), NB, sp);
+        const bool push = p2p && K + 1 < nblk;
+        float* pc = push ? box_crit(c->peer_pbox, pq(K)) : nullptr;
+        launch_ext_finish(c->ext, lde, kb, A11, ld, c->il[0], c->il[1], iut_hi(b), iut_lo(b), NB,
+                          pc, pc ? pc + nb2 : nullptr, c->push_counters, push ? reinterpret_cast<unsigned*>(c->peer_pbox) : nullptr, seq_of(K), sp);
         CK(cudaEventRecord(c->ev_inv[b], sp));
         return GAUSS_CUDA_OK;
     };
@@ -1114,7 +1212,10 @@ static int factor_cp(gauss_cuda_ctx* c)
             // U[K, K+1]^T = A12^T inv(L11)^T  (kb_next x kb), raw into ut[b], then split into the crit package
             if ((rc = gemm_tc(c, sp, c->a12t[0] + (size_t)c1 * NB, c->a12t[1] + (size_t)c1 * NB, NB, c->il[0], c->il[1], NB,
                               c->ut[b] + (size_t)c1 * NB, NB, ccrit, kb, kb, +1, 0))) return rc;
-            launch_split_rowmajor(c->ut[b] + (size_t)c1 * NB, NB, uc_hi(b), uc_lo(b), NB, ccrit, kb, sp);
+            float* pc = p2p ? box_crit(c->peer_pbox, pq(K)) : nullptr;
+            launch_crit_split(c->ut[b] + (size_t)c1 * NB, NB, uc_hi(b), uc_lo(b), NB, ccrit, kb,
+                              pc ? pc + 2 * nb2 : nullptr, pc ? pc + 3 * nb2 : nullptr, c->push_counters + 8,
+                              p2p ? reinterpret_cast<unsigned*>(c->peer_pbox) + 32 : nullptr, seq_of(K), sp);
             CK(cudaEventRecord(c->ev_critlocal[b], sp));
             if (c->trace && K > 0) cudaEventRecord(c->tr_ev[8 * (size_t)(K - 1) + 4], sp);
         } else {
@@ -1188,30 +1289,55 @@ static int factor_cp(gauss_cuda_ctx* c)
         const int rows_next = blk_rows(c, K + 1), cnext = k0 + kb;
         const bool own_next = owner_of(K + 1) == c->rank;
         const int l0 = first_local_block_after(c, K) * NB;          // first local row below block K
-        const int m = c->rows_local - l0;
         const int l1 = own_next ? l0 + rows_next : l0;              // first local row below block K+1
-        float* Wb = c->W + (size_t)l0 * ld;
 
         auto mark = [&](int i, cudaStream_t st) { if (c->trace) cudaEventRecord(c->tr_ev[8 * (size_t)K + i], st); };
         // 1. side stream: L21 = A21 inv(U11) (+ split), columns of block K+1, next A21 split
-        CK(cudaStreamWaitEvent(ss, c->ev_crit[b], 0));
+        // the next owner reads crit(K) from its peer box (pushed by the owner of K), everyone else from the broadcast
+        const bool from_box = p2p && own_next;
+        const float* c_iut_hi = from_box ? box_crit(c->pbox, pq(K)) : iut_hi(b);
+        const float* c_iut_lo = c_iut_hi + nb2;
+        const float* c_uc_hi = c_iut_hi + 2 * nb2;
+        const float* c_uc_lo = c_iut_hi + 3 * nb2;
+        if (from_box) { if ((rc = wait_flag(ss, 0, seq_of(K)))) return rc; }
+        else CK(cudaStreamWaitEvent(ss, c->ev_crit[b], 0));
         CK(cudaStreamWaitEvent(ss, c->ev_free[b], 0));              // la[b] of step K-2 no longer read by its bulk update
         mark(0, ss);
-        if (m > 0) {
-            if ((rc = gemm_tc(c, ss, c->as_[0] + (size_t)l0 * NB, c->as_[1] + (size_t)l0 * NB, NB, iut_hi(b), iut_lo(b), NB,
-                              Wb + k0, ld, m, kb, kb, +1, 0))) return rc;
-            launch_split_rowmajor(Wb + k0, ld, c->la_hi[b] + (size_t)l0 * NB, c->la_lo[b] + (size_t)l0 * NB, NB, m, kb, ss);
-        }
-        CK(cudaEventRecord(c->ev_la[b], ss));
-        mark(1, ss);
+        // L21 of rows [ra, rb) (local), then their columns of block K+1
+        auto l21_rows = [&](int ra, int rb) -> int {
+            if (rb <= ra) return GAUSS_CUDA_OK;
+            float* Wr = c->W + (size_t)ra * ld;
+            int r2 = gemm_tc(c, ss, c->as_[0] + (size_t)ra * NB, c->as_[1] + (size_t)ra * NB, NB, c_iut_hi, c_iut_lo, NB,
+                             Wr + k0, ld, rb - ra, kb, kb, +1, 0);
+            if (r2) return r2;
+            launch_split_rowmajor(Wr + k0, ld, c->la_hi[b] + (size_t)ra * NB, c->la_lo[b] + (size_t)ra * NB, NB, rb - ra, kb, ss);
+            return GAUSS_CUDA_OK;
+        };
+        auto colstrip_rows = [&](int ra, int rb) -> int {
+            if (rb <= ra) return GAUSS_CUDA_OK;
+            return gemm_tc(c, ss, c->la_hi[b] + (size_t)ra * NB, c->la_lo[b] + (size_t)ra * NB, NB, c_uc_hi, c_uc_lo, NB,
+                           c->W + (size_t)ra * ld + cnext, ld, rb - ra, rows_next, kb, -1, 1);
+        };
         // block column K+1 has received panel K-1's contribution through the bulk update of step K-1: that must be complete
         // before this step's contribution is added and the column is read (next A21 split, next diagonal region)
-        CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
-        if (m > 0) {
-            if ((rc = gemm_tc(c, ss, c->la_hi[b] + (size_t)l0 * NB, c->la_lo[b] + (size_t)l0 * NB, NB, uc_hi(b), uc_lo(b), NB,
-                              Wb + cnext, ld, m, rows_next, kb, -1, 1))) return rc;
+        if (own_next) {                                            // the rows of block K+1 first: they complete the next diagonal region
+            if ((rc = l21_rows(l0, l1))) return rc;
+            CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
+            if (from_box && (rc = wait_flag(ss, 32, seq_of(K)))) return rc;
+            if ((rc = colstrip_rows(l0, l1))) return rc;
+            CK(cudaEventRecord(c->ev_colstrip[b], ss));
+            mark(1, ss);
+            if ((rc = l21_rows(l1, c->rows_local))) return rc;
+            CK(cudaEventRecord(c->ev_la[b], ss));
+            if ((rc = colstrip_rows(l1, c->rows_local))) return rc;
+        } else {
+            if ((rc = l21_rows(l0, c->rows_local))) return rc;
+            CK(cudaEventRecord(c->ev_la[b], ss));
+            mark(1, ss);
+            CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
+            if ((rc = colstrip_rows(l0, c->rows_local))) return rc;
+            CK(cudaEventRecord(c->ev_colstrip[b], ss));
         }
-        CK(cudaEventRecord(c->ev_colstrip[b], ss));
         CK(cudaEventRecord(c->ev_critfree[b], ss));
         mark(2, ss);
         if (c->rows_local - l1 > 0 && K + 2 < nblk)
@@ -1244,7 +1370,9 @@ static int factor_cp(gauss_cuda_ctx* c)
         // 5. communication of step K+1
         if ((rc = comm(K + 1))) return rc;
         // 6. bulk of the trailing update (CTAs give up their SM every few tiles: the other streams have priority)
-        if ((rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1, c->overlap_max_tiles))) return rc;
+        if (!c->cp_nobulk &&
+            (rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1,
+                                  c->cp_reserve > 0 ? 0 : c->overlap_max_tiles, c->cp_reserve))) return rc;
         CK(cudaEventRecord(c->ev_free[b], s));
         mark(5, s);
     }
@@ -1372,7 +1500,7 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
         };
         for (int K = 0; K + 1 < c->nblk; ++K) {
             el2(K, 0, K, 1, a_p2); el2(K, 1, K, 2, a_cs);
-            if (K % c->world == (c->rank + c->world - 1) % c->world && el2(K, 2, K, 3, a_chain)) ++n_chain;
+            if (K % c->world == (c->rank + c->world - 1) % c->world && el2(K, 1, K, 3, a_chain)) ++n_chain;
             if (K % c->world == (c->rank + c->world - 1) % c->world) el2(K, 3, K, 4, a_cu);
             if (c->world == 1) el2(K, 4, K + 1, 0, a_hand);
             el2(K, 0, K + 1, 0, a_crit2crit);

@@ -71,8 +71,15 @@ int  tc_setup_device(bool reread_env = true);   // same for the tile engine; ret
 // E[0:2kb, 0:2kb] <- [[A11, I], [I, 0]]; after the in-panel chain on E: [[L11|U11, inv(L11)], [inv(U11), *]].
 void launch_ext_prepare(const float* a11, int ld, float* E, int lde, int kb, cudaStream_t s);
 // L11|U11 back into the matrix; il_* = hi/lo split of inv(L11) (row-major, ldo); iut_* = hi/lo split of inv(U11)^T.
+// peer_* (may be null): the next owner's copy of iut_* in peer-mapped memory; peer_flag (may be null): word in the peer's
+// memory set to `seq` once every CTA's stores are out; counter: one zeroed device word per launch site.
 void launch_ext_finish(const float* E, int lde, int kb, float* a11, int ld,
-                       float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo, cudaStream_t s);
+                       float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo,
+                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s);
+// hi/lo split of a row-major block into local (and peer) operand buffers, then the peer's flag
+void launch_crit_split(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols,
+                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s);
+void launch_wait_flag(const unsigned* flag, unsigned value, cudaStream_t s);
 
 // ---- partial-pivoting panel (lu_pivot.cu) --------------------------------------------------
 // Factors the panel W[k0.., k0..k0+128) of an [np x ld] single-GPU system with row interchanges
@@ -98,6 +105,9 @@ void tc_set_pair_ok(bool ok);       // false: this thread's launches must use th
 // > 0: CTAs of this thread's following tc_gemm_nt launches exit after that many tiles (the grid grows to match),
 // so kernels of other streams get SMs while a long launch runs.  0 = persistent CTAs.
 void tc_set_max_tiles(int max_tiles);
+// > 0: this thread's following tc_gemm_nt launches use at most (SM count - n) SMs, so that the small kernels of a
+// latency-bound chain on another stream always find a free SM while a long update runs.
+void tc_set_reserve_sms(int n);
 
 extern thread_local long long g_launch_count;   // kernels launched by this thread since last reset
 

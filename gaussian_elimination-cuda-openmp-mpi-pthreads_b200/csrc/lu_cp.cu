@@ -10,9 +10,34 @@
 // to the identity columns is L11^-1, the L-col solve applied to the identity rows is U11^-1.  With them the two panel
 // solves of the outer block become single GEMMs on the tile engine (L21 = A21 inv(U11), U12 = inv(L11) A12) instead
 // of 2 x kb/128 dependent launches, which is what shortens the multi-GPU critical path.
+//
+// Fused with their collective: the two kernels that produce the "crit" package (ext_finish: inv(U11)^T split; crit_split:
+// U[K, K+1]^T split) store it straight into the NEXT owner's receive buffer as well -- plain st.global on a peer mapping
+// over NVLink, no TMA involved -- and the last CTA to finish publishes a sequence number in the peer's flag word
+// (fence.sys + st.release.sys).  The receiver's stream waits on that word.  This replaces, on the critical path, the
+// reference's per-step MPI_Bcast of the pivot row (gauss_mpi/gauss_internal_input.c:135-137) for the one rank that needs
+// the data first; everyone else still gets it by the NCCL broadcast, with a step of slack.
 #include "gauss_internal.cuh"
+#include <stdio.h>
 
 namespace gb200 {
+
+// Called by every thread of every CTA at the end of a kernel that wrote to peer memory: the last CTA to arrive stores
+// `value` into `flag` (a word in the peer's memory) after all CTAs' stores have been made visible system-wide.
+__device__ __forceinline__ void signal_peer_when_done(unsigned* counter, unsigned nblocks, unsigned* flag, unsigned value)
+{
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && threadIdx.y == 0) {
+        __threadfence_system();
+        const unsigned prev = atomicAdd(counter, 1u);
+        if (prev == nblocks - 1) {
+            *counter = 0;                                     // rearm for the next launch (stream order makes it visible)
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+        }
+    }
+}
 
 __device__ __forceinline__ void cp_split(float x, float& hi, float& lo)
 {
@@ -58,7 +83,8 @@ void launch_ext_prepare(const float* a11, int ld, float* E, int lde, int kb, cud
 // 32 x 32 tiles, 32 x 8 threads.
 __global__ void __launch_bounds__(256)
 ext_finish_kernel(const float* __restrict__ E, int lde, int kb, float* __restrict__ a11, int ld,
-                  float* __restrict__ il_hi, float* __restrict__ il_lo, float* __restrict__ iut_hi, float* __restrict__ iut_lo, int ldo)
+                  float* __restrict__ il_hi, float* __restrict__ il_lo, float* __restrict__ iut_hi, float* __restrict__ iut_lo, int ldo,
+                  float* __restrict__ peer_hi, float* __restrict__ peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq)
 {
     __shared__ float t[32][33];
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -83,15 +109,70 @@ ext_finish_kernel(const float* __restrict__ E, int lde, int kb, float* __restric
             cp_split(t[tx][i], h, l);                            // element (row r0+tx, column c0+i) -> out[c0+i][r0+tx]
             iut_hi[(size_t)(c0 + i) * ldo + r0 + tx] = h;
             iut_lo[(size_t)(c0 + i) * ldo + r0 + tx] = l;
+            if (peer_hi != nullptr) {                            // the next owner's copy, over NVLink
+                peer_hi[(size_t)(c0 + i) * ldo + r0 + tx] = h;
+                peer_lo[(size_t)(c0 + i) * ldo + r0 + tx] = l;
+            }
         }
     }
+    if (peer_flag != nullptr) signal_peer_when_done(counter, gridDim.x * gridDim.y, peer_flag, seq);
 }
 
 void launch_ext_finish(const float* E, int lde, int kb, float* a11, int ld,
-                       float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo, cudaStream_t s)
+                       float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo,
+                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s)
 {
     dim3 grid(kb / 32, 2 * (kb / 32));
-    ext_finish_kernel<<<grid, dim3(32, 8), 0, s>>>(E, lde, kb, a11, ld, il_hi, il_lo, iut_hi, iut_lo, ldo);
+    ext_finish_kernel<<<grid, dim3(32, 8), 0, s>>>(E, lde, kb, a11, ld, il_hi, il_lo, iut_hi, iut_lo, ldo, peer_hi, peer_lo, counter, peer_flag, seq);
+    ++g_launch_count;
+}
+
+// hi/lo[r][c] = split(src[r][c]) for r < rows, c < cols (cols a multiple of 4), written to the local operand buffers and,
+// when given, to the next owner's; then the peer's flag word is set to `seq`.
+__global__ void __launch_bounds__(128)
+crit_split_kernel(const float* __restrict__ src, int lds, float* __restrict__ hi, float* __restrict__ lo, int ldd, int rows, int cols,
+                  float* __restrict__ peer_hi, float* __restrict__ peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq)
+{
+    const int c4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    const int r = blockIdx.y;
+    if (c4 < cols && r < rows) {
+        const float4 v = *reinterpret_cast<const float4*>(src + (size_t)r * lds + c4);
+        float4 h, l;
+        cp_split(v.x, h.x, l.x); cp_split(v.y, h.y, l.y); cp_split(v.z, h.z, l.z); cp_split(v.w, h.w, l.w);
+        *reinterpret_cast<float4*>(hi + (size_t)r * ldd + c4) = h;
+        *reinterpret_cast<float4*>(lo + (size_t)r * ldd + c4) = l;
+        if (peer_hi != nullptr) {
+            *reinterpret_cast<float4*>(peer_hi + (size_t)r * ldd + c4) = h;
+            *reinterpret_cast<float4*>(peer_lo + (size_t)r * ldd + c4) = l;
+        }
+    }
+    if (peer_flag != nullptr) signal_peer_when_done(counter, gridDim.x * gridDim.y, peer_flag, seq);
+}
+
+void launch_crit_split(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols,
+                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s)
+{
+    dim3 grid((cols / 4 + 127) / 128, rows);
+    crit_split_kernel<<<grid, 128, 0, s>>>(src, lds, hi, lo, ldd, rows, cols, peer_hi, peer_lo, counter, peer_flag, seq);
+    ++g_launch_count;
+}
+
+// Fallback for drivers without stream memory operations: one warp spins (bounded) until *flag >= value.
+__global__ void wait_flag_kernel(const unsigned* flag, unsigned value)
+{
+    if (threadIdx.x != 0) return;
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flag) : "memory");
+        if ((int)(v - value) >= 0) break;
+        if (clock64() - t0 > 20000000000LL) { printf("gauss_cuda: peer flag wait timed out (have %u, want %u)\n", v, value); __trap(); }
+        __nanosleep(100);
+    }
+}
+void launch_wait_flag(const unsigned* flag, unsigned value, cudaStream_t s)
+{
+    wait_flag_kernel<<<1, 32, 0, s>>>(flag, value);
     ++g_launch_count;
 }
 

@@ -668,6 +668,7 @@ static unsigned g_sched_next = 0;
 // on different streams can never share one); everyone else uses the library's ring.
 static thread_local int* t_sched_override = nullptr;
 static thread_local int t_max_tiles = 0;
+static thread_local int t_reserve_sms = 0;   // SMs this thread's following launches leave free (bulk updates beside a latency-bound panel chain)
 constexpr int g_dynamic = 1;         // tiles come from the dynamic scheduler (static round-robin was measured and dropped)
 static int g_reserve_sms = 0;        // SMs left free for concurrent kernels (NCCL broadcast of the look-ahead panel)
 static int g_pair = 1;               // GAUSS_CUDA_TC_PAIR=0 switches the CTA-pair kernel off
@@ -742,7 +743,7 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     rc |= make_map(&tc, C, n, m, ldc, TEPI_W, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return (int)cudaErrorInvalidValue;
     const int tiles = ((m + TBM - 1) / TBM) * ((n + TBN - 1) / TBN);
-    const int avail = g_num_sms - g_reserve_sms;
+    const int avail = g_num_sms - std::max(g_reserve_sms, t_reserve_sms);
     int grid = tiles < avail ? tiles : avail;
     int dyn = (g_dynamic && tiles > grid) ? 1 : 0;
     int max_tiles = 0;
@@ -776,7 +777,7 @@ static int launch_pair(const float* Ahi, const float* Alo, int lda, const float*
     rc |= make_map(&tc, C, n, m, ldc, TEPI_W, TBM, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return (int)cudaErrorInvalidValue;
     const int tiles = ((m + TBM2 - 1) / TBM2) * ((n + TBN - 1) / TBN);
-    const int avail = (g_num_sms - g_reserve_sms) / 2;
+    const int avail = (g_num_sms - std::max(g_reserve_sms, t_reserve_sms)) / 2;
     int pairs = std::min(tiles, avail);
     int dyn = (g_dynamic && tiles > pairs) ? 1 : 0;
     int max_tiles = 0;
@@ -798,6 +799,7 @@ static int launch_pair(const float* Ahi, const float* Alo, int lda, const float*
 void tc_set_pair_ok(bool ok) { t_pair_ok = ok; }
 void tc_set_sched_slots(int* slots) { t_sched_override = slots; }
 void tc_set_max_tiles(int max_tiles) { t_max_tiles = max_tiles; }
+void tc_set_reserve_sms(int n) { t_reserve_sms = n < 0 ? 0 : (n > 100 ? 100 : n); }
 
 int tc_gemm_nt(const float* Ahi, const float* Alo, int lda, const float* Bhi, const float* Blo, int ldb,
                float* C, int ldc, int m, int n, int k, int sign, int beta, cudaStream_t s)
