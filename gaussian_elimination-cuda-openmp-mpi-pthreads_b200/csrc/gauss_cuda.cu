@@ -203,6 +203,9 @@ struct gauss_cuda_ctx {
     unsigned* push_counters = nullptr;          // device: completion counters of the two pushing kernels
     unsigned solve_seq = 0;                     // factorisations run by this context (every rank counts alike): flag values are seq * nblk + K + 1
     bool memops = false;                        // cuStreamWaitValue32 available (else a spinning one-warp kernel waits)
+    int cp_near = 3;                            // outer blocks after the crit block whose U12^T travels (and is applied) ahead of the rest (GAUSS_CUDA_CP_NEAR)
+    cudaEvent_t ev_near[2] = {nullptr, nullptr}, ev_nearlocal[2] = {nullptr, nullptr}, ev_rownear[2] = {nullptr, nullptr};
+    bool pdl = true;                            // GAUSS_CUDA_PDL=0: the chain's kernels are launched without programmatic dependent launch
     bool cp_nobulk = false;                     // GAUSS_CUDA_CP_NOBULK=1: timing diagnostic only (WRONG results): the bulk update is skipped
     float* ext = nullptr;                       // [2NB x 2NB] extended scratch E
     float* ext_la[2] = {nullptr, nullptr};      // hi/lo [2NB x NB]  split L of the chain inside E
@@ -330,6 +333,11 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         c->cp = want && mode == GAUSS_CUDA_MODE_3XTF32;
         const char* r = getenv("GAUSS_CUDA_CP_RESERVE");
         if (r) c->cp_reserve = std::max(0, std::min(64, atoi(r)));
+        if (!r) c->cp_reserve = world >= 4 ? 32 : 16;
+        const char* pd = getenv("GAUSS_CUDA_PDL");
+        if (pd) c->pdl = atoi(pd) != 0;
+        const char* nr = getenv("GAUSS_CUDA_CP_NEAR");
+        if (nr) c->cp_near = std::max(1, std::min(64, atoi(nr)));
         const char* nbk = getenv("GAUSS_CUDA_CP_NOBULK");
         c->cp_nobulk = nbk && atoi(nbk) != 0;
     }
@@ -415,7 +423,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         cudaEvent_t* evs[] = {&c->ev_crit[0], &c->ev_crit[1], &c->ev_critlocal[0], &c->ev_critlocal[1], &c->ev_critfree[0], &c->ev_critfree[1],
                               &c->ev_ut[0], &c->ev_ut[1], &c->ev_utlocal[0], &c->ev_utlocal[1], &c->ev_utfree[0], &c->ev_utfree[1],
                               &c->ev_la[0], &c->ev_la[1], &c->ev_colstrip[0], &c->ev_colstrip[1], &c->ev_rowrest[0], &c->ev_rowrest[1],
-                              &c->ev_inv[0], &c->ev_inv[1], &c->ev_p4a, &c->ev_wjoin};
+                              &c->ev_inv[0], &c->ev_inv[1], &c->ev_p4a, &c->ev_wjoin,
+                              &c->ev_near[0], &c->ev_near[1], &c->ev_nearlocal[0], &c->ev_nearlocal[1], &c->ev_rownear[0], &c->ev_rownear[1]};
         for (cudaEvent_t* ev : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
     }
     if (world > 1 || c->cp) {
@@ -492,7 +501,8 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
         cudaEvent_t evs[] = {c->ev_crit[0], c->ev_crit[1], c->ev_critlocal[0], c->ev_critlocal[1], c->ev_critfree[0], c->ev_critfree[1],
                              c->ev_ut[0], c->ev_ut[1], c->ev_utlocal[0], c->ev_utlocal[1], c->ev_utfree[0], c->ev_utfree[1],
                              c->ev_la[0], c->ev_la[1], c->ev_colstrip[0], c->ev_colstrip[1], c->ev_rowrest[0], c->ev_rowrest[1],
-                             c->ev_inv[0], c->ev_inv[1], c->ev_p4a, c->ev_wjoin};
+                             c->ev_inv[0], c->ev_inv[1], c->ev_p4a, c->ev_wjoin,
+                             c->ev_near[0], c->ev_near[1], c->ev_nearlocal[0], c->ev_nearlocal[1], c->ev_rownear[0], c->ev_rownear[1]};
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
     }
     if (c->peer_pbox) cudaIpcCloseMemHandle(c->peer_pbox);
@@ -1159,6 +1169,8 @@ static int factor_cp(gauss_cuda_ctx* c)
     auto iut_lo = [&](int b) { return c->crit[b] + nb2; };
     auto uc_hi = [&](int b) { return c->crit[b] + 2 * nb2; };
     auto uc_lo = [&](int b) { return c->crit[b] + 3 * nb2; };
+    // columns right of block K: [crit block K+1 | near: the next cp_near blocks | far: the rest]; near_end = first far column
+    auto near_end = [&](int K) { return std::min(ld, (K + 2 + c->cp_near) * NB); };
     int rc;
     // peer push: the owner of K stores crit(K) into the box of the owner of K+1 (always the next rank); the receiver
     // double-buffers by the parity of its own use count ((K+1) / world) and waits for flag words 0 (inv(U11)^T) and 32 (U^T)
@@ -1181,6 +1193,7 @@ static int factor_cp(gauss_cuda_ctx* c)
     auto panel_diag = [&](int K) -> int {
         const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
         float* A11 = c->W + (size_t)blk_local_row(c, K) * ld + k0;
+        PdlScope pdl_on(c->pdl);                                    // the chain's kernels release each other early
         CK(cudaStreamWaitEvent(sp, c->ev_critfree[b], 0));        // crit[b] (iut) of step K-2 has been consumed here
         launch_ext_prepare(A11, ld, c->ext, lde, kb, sp);
         if ((rc = ext_chain(c, k0, kb, sp))) return rc;
@@ -1201,11 +1214,12 @@ static int factor_cp(gauss_cuda_ctx* c)
         float* P = c->W + (size_t)blk_local_row(c, K) * ld;       // the row panel (kb rows)
         const int ccrit = (K + 1 < nblk) ? blk_rows(c, K + 1) : 0;  // columns of block K+1
         CK(cudaStreamWaitEvent(sp, c->ev_wjoin, 0));              // a12t is single-buffered too (previous row panel on the wide stream)
-        if (have_rowrest) {
-            CK(cudaStreamWaitEvent(sp, c->ev_rowrest[b ^ 1], 0));
+        if (have_rowrest) {                                        // the crit columns only need the near part of the previous step
+            CK(cudaStreamWaitEvent(sp, c->ev_rownear[b ^ 1], 0));
             CK(cudaStreamWaitEvent(sw, c->ev_rowrest[b ^ 1], 0));
         }
         if (ccrit > 0) {
+            PdlScope pdl_on(c->pdl);
             CK(cudaStreamWaitEvent(sp, c->ev_utfree[b], 0));        // ut[b] of step K-2 has been split everywhere it is read here
             launch_split_transpose(P + c1, ld, c->a12t[0] + (size_t)c1 * NB, c->a12t[1] + (size_t)c1 * NB, NB, kb, ccrit, kb, sp);
             CK(cudaEventRecord(c->ev_p4a, sp));
@@ -1224,15 +1238,21 @@ static int factor_cp(gauss_cuda_ctx* c)
         // the rest of the row panel on the wide stream
         CK(cudaStreamWaitEvent(sw, c->ev_inv[b], 0));
         CK(cudaStreamWaitEvent(sw, c->ev_utfree[b], 0));
-        const int crest = c1 + ccrit, nrest = ld - crest;
-        if (nrest > 0) {
-            launch_split_transpose(P + crest, ld, c->a12t[0] + (size_t)crest * NB, c->a12t[1] + (size_t)crest * NB, NB, kb, nrest, kb, sw);
-            if (K + 1 < nblk) {
-                if ((rc = gemm_tc(c, sw, c->a12t[0] + (size_t)crest * NB, c->a12t[1] + (size_t)crest * NB, NB, c->il[0], c->il[1], NB,
-                                  c->ut[b] + (size_t)crest * NB, NB, nrest, kb, kb, +1, 0))) return rc;
+        const int crest = c1 + ccrit, cn = std::max(crest, near_end(K));
+        for (int part = 0; part < 2; ++part) {                     // near columns, then far columns
+            const int ca = part ? cn : crest, cb = part ? ld : cn;
+            if (cb > ca) {
+                launch_split_transpose(P + ca, ld, c->a12t[0] + (size_t)ca * NB, c->a12t[1] + (size_t)ca * NB, NB, kb, cb - ca, kb, sw);
+                if (K + 1 < nblk) {
+                    if ((rc = gemm_tc(c, sw, c->a12t[0] + (size_t)ca * NB, c->a12t[1] + (size_t)ca * NB, NB, c->il[0], c->il[1], NB,
+                                      c->ut[b] + (size_t)ca * NB, NB, cb - ca, kb, kb, +1, 0))) return rc;
+                }
+            }
+            if (part == 0) {
+                CK(cudaStreamWaitEvent(sw, c->ev_critlocal[b], 0)); // (the crit rows of ut[b] travel with the near payload)
+                CK(cudaEventRecord(c->ev_nearlocal[b], sw));
             }
         }
-        CK(cudaStreamWaitEvent(sw, c->ev_critlocal[b], 0));         // (the crit rows of ut[b] are part of the bulk payload)
         CK(cudaEventRecord(c->ev_utlocal[b], sw));
         // U12 itself, in place, for back substitution (solveGauss reads the owner's rows): inv(L11) A12
         CK(cudaStreamWaitEvent(sw, c->ev_p4a, 0));
@@ -1253,11 +1273,20 @@ static int factor_cp(gauss_cuda_ctx* c)
             if (!mine) c->bcast_bytes += 4.0 * nb2 * sizeof(float);
         }
         CK(cudaEventRecord(c->ev_crit[b], sc));
-        if (mine) CK(cudaStreamWaitEvent(sc, c->ev_utlocal[b], 0));
+        // U12^T: the near columns (crit block included) first, the far columns second
+        const int cn = std::max(c1, near_end(K));
+        if (mine) CK(cudaStreamWaitEvent(sc, c->ev_nearlocal[b], 0));
         else      CK(cudaStreamWaitEvent(sc, c->ev_utfree[b], 0));
         if (c->world > 1) {
-            const size_t cnt = (size_t)(ld - c1) * NB;
+            const size_t cnt = (size_t)(cn - c1) * NB;
             NK(g_nccl.Broadcast(c->ut[b] + (size_t)c1 * NB, c->ut[b] + (size_t)c1 * NB, cnt, ncclFloat, owner_of(K), c->comm, sc));
+            if (!mine) c->bcast_bytes += (double)cnt * sizeof(float);
+        }
+        CK(cudaEventRecord(c->ev_near[b], sc));
+        if (mine) CK(cudaStreamWaitEvent(sc, c->ev_utlocal[b], 0));
+        if (c->world > 1 && ld > cn) {
+            const size_t cnt = (size_t)(ld - cn) * NB;
+            NK(g_nccl.Broadcast(c->ut[b] + (size_t)cn * NB, c->ut[b] + (size_t)cn * NB, cnt, ncclFloat, owner_of(K), c->comm, sc));
             if (!mine) c->bcast_bytes += (double)cnt * sizeof(float);
         }
         CK(cudaEventRecord(c->ev_ut[b], sc));
@@ -1321,6 +1350,7 @@ static int factor_cp(gauss_cuda_ctx* c)
         // block column K+1 has received panel K-1's contribution through the bulk update of step K-1: that must be complete
         // before this step's contribution is added and the column is read (next A21 split, next diagonal region)
         if (own_next) {                                            // the rows of block K+1 first: they complete the next diagonal region
+            PdlScope pdl_on(c->pdl);
             if ((rc = l21_rows(l0, l1))) return rc;
             CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
             if (from_box && (rc = wait_flag(ss, 32, seq_of(K)))) return rc;
@@ -1352,16 +1382,24 @@ static int factor_cp(gauss_cuda_ctx* c)
         }
 
         // 3. main stream: U12^T of step K arrives -> B operand; the rest of block K+1's rows
-        CK(cudaStreamWaitEvent(s, c->ev_ut[b], 0));
-        mark(6, s);
-        launch_split_rowmajor(c->ut[b] + (size_t)cnext * NB, NB, c->ub_hi[b] + (size_t)cnext * NB, c->ub_lo[b] + (size_t)cnext * NB, NB,
-                              ld - cnext, kb, s);
-        CK(cudaEventRecord(c->ev_utfree[b], s));
-        CK(cudaStreamWaitEvent(s, c->ev_la[b], 0));
+        const int cn = std::max(cnext, near_end(K)), cfirst = cnext + rows_next;    // first far column, first column right of block K+1
         const PanelRef pr{nullptr, 0, nullptr, 0, c->ub_hi[b], c->ub_lo[b]};
         const StepBufs sbm{s, c->la_hi[b], c->la_lo[b]};
+        CK(cudaStreamWaitEvent(s, c->ev_near[b], 0));
+        launch_split_rowmajor(c->ut[b] + (size_t)cnext * NB, NB, c->ub_hi[b] + (size_t)cnext * NB, c->ub_lo[b] + (size_t)cnext * NB, NB,
+                              cn - cnext, kb, s);
+        CK(cudaStreamWaitEvent(s, c->ev_la[b], 0));
+        if (own_next) {                                            // near columns of block K+1's rows: all its crit columns depend on
+            if (cn > cfirst && (rc = trailing_update(c, K, pr, sbm, l0, l1, cfirst, cn - cfirst))) return rc;
+            CK(cudaEventRecord(c->ev_rownear[b], s));
+        }
+        CK(cudaStreamWaitEvent(s, c->ev_ut[b], 0));
+        mark(6, s);
+        if (ld > cn)
+            launch_split_rowmajor(c->ut[b] + (size_t)cn * NB, NB, c->ub_hi[b] + (size_t)cn * NB, c->ub_lo[b] + (size_t)cn * NB, NB, ld - cn, kb, s);
+        CK(cudaEventRecord(c->ev_utfree[b], s));
         if (own_next) {
-            if ((rc = trailing_update(c, K, pr, sbm, l0, l1, cnext + rows_next, -1))) return rc;
+            if (ld > std::max(cn, cfirst) && (rc = trailing_update(c, K, pr, sbm, l0, l1, std::max(cn, cfirst), -1))) return rc;
             CK(cudaEventRecord(c->ev_rowrest[b], s));
             // 4. the row panel of block K+1: crit package first, wide part beside it
             if ((rc = panel_row(K + 1, true))) return rc;

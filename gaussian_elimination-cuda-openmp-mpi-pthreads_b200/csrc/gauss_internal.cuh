@@ -111,4 +111,28 @@ void tc_set_reserve_sms(int n);
 
 extern thread_local long long g_launch_count;   // kernels launched by this thread since last reset
 
+// ---- programmatic dependent launch (PDL) ----------------------------------------------------
+// The panel chain is a string of short dependent kernels; between two of them the GPU otherwise pays the drain of the
+// first, the launch of the second and the second's prologue (barrier / TMEM set-up, tensor-map fetch).  Kernels of the
+// chain therefore (a) release their dependents at once (griddepcontrol.launch_dependents at the top) and (b) wait for
+// their predecessors' memory only where they first touch global data (griddepcontrol.wait).  Both instructions are
+// no-ops in a launch without the attribute, which is how every other launch of the same kernels runs.
+extern thread_local bool t_pdl;                 // this thread's following launch_k calls carry the PDL attribute
+struct PdlScope { bool prev; explicit PdlScope(bool on) : prev(t_pdl) { t_pdl = on; } ~PdlScope() { t_pdl = prev; } };
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = t_pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 } // namespace gb200

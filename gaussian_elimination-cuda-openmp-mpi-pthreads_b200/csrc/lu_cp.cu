@@ -54,6 +54,8 @@ ext_prepare_kernel(const float* __restrict__ a11, int ld, float* __restrict__ E,
 {
     const int c4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int r = blockIdx.y;
+    pdl_release();
+    pdl_wait();
     if (c4 >= 2 * kb) return;
     float4 v;
     if (r < kb && c4 < kb) {
@@ -71,7 +73,7 @@ ext_prepare_kernel(const float* __restrict__ a11, int ld, float* __restrict__ E,
 void launch_ext_prepare(const float* a11, int ld, float* E, int lde, int kb, cudaStream_t s)
 {
     dim3 grid((2 * kb / 4 + 255) / 256, 2 * kb);
-    ext_prepare_kernel<<<grid, 256, 0, s>>>(a11, ld, E, lde, kb);
+    launch_k(ext_prepare_kernel, grid, dim3(256), 0, s, a11, ld, E, lde, kb);
     ++g_launch_count;
 }
 
@@ -90,6 +92,8 @@ ext_finish_kernel(const float* __restrict__ E, int lde, int kb, float* __restric
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int c0 = blockIdx.x * 32;
     const int nby = kb / 32;
+    pdl_release();
+    pdl_wait();
     if ((int)blockIdx.y < nby) {
         const int r0 = blockIdx.y * 32;
         for (int i = ty; i < 32; i += 8) {
@@ -123,7 +127,7 @@ void launch_ext_finish(const float* E, int lde, int kb, float* a11, int ld,
                        float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s)
 {
     dim3 grid(kb / 32, 2 * (kb / 32));
-    ext_finish_kernel<<<grid, dim3(32, 8), 0, s>>>(E, lde, kb, a11, ld, il_hi, il_lo, iut_hi, iut_lo, ldo, peer_hi, peer_lo, counter, peer_flag, seq);
+    launch_k(ext_finish_kernel, grid, dim3(32, 8), 0, s, E, lde, kb, a11, ld, il_hi, il_lo, iut_hi, iut_lo, ldo, peer_hi, peer_lo, counter, peer_flag, seq);
     ++g_launch_count;
 }
 
@@ -135,6 +139,8 @@ crit_split_kernel(const float* __restrict__ src, int lds, float* __restrict__ hi
 {
     const int c4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int r = blockIdx.y;
+    pdl_release();
+    pdl_wait();
     if (c4 < cols && r < rows) {
         const float4 v = *reinterpret_cast<const float4*>(src + (size_t)r * lds + c4);
         float4 h, l;
@@ -153,7 +159,7 @@ void launch_crit_split(const float* src, int lds, float* hi, float* lo, int ldd,
                        float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s)
 {
     dim3 grid((cols / 4 + 127) / 128, rows);
-    crit_split_kernel<<<grid, 128, 0, s>>>(src, lds, hi, lo, ldd, rows, cols, peer_hi, peer_lo, counter, peer_flag, seq);
+    launch_k(crit_split_kernel, grid, dim3(128), 0, s, src, lds, hi, lo, ldd, rows, cols, peer_hi, peer_lo, counter, peer_flag, seq);
     ++g_launch_count;
 }
 

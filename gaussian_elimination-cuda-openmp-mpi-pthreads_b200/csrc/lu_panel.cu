@@ -222,7 +222,9 @@ diag_factor_pair_kernel(float* __restrict__ blk, int ld, int grow0, int* __restr
 {
     __shared__ DiagSmem2 sm;
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    pdl_release();
     if (tid == 0) sm.first_bad = kNb;
+    pdl_wait();
     float a[8][8];
 #pragma unroll
     for (int p = 0; p < 8; ++p)
@@ -257,7 +259,7 @@ void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaSt
 {
     if (g_diag_variant < 0) { const char* e = getenv("GAUSS_CUDA_DIAG"); g_diag_variant = e ? atoi(e) : 2; }
     if (g_diag_variant == 0) diag_factor_kernel<<<1, 256, 0, s>>>(blk, ld, global_row0, status);
-    else diag_factor_pair_kernel<<<1, 256, 0, s>>>(blk, ld, global_row0, status);
+    else launch_k(diag_factor_pair_kernel, dim3(1), dim3(256), 0, s, blk, ld, global_row0, status);
     ++g_launch_count;
 }
 
@@ -808,6 +810,8 @@ urow_mma_kernel(const float* __restrict__ l11, int ldl, float* __restrict__ a12,
                 float* __restrict__ ub_hi, float* __restrict__ ub_lo, int ldub, int k_ub)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    pdl_release();
+    pdl_wait();
     urow_mma_body(smem_raw, blockIdx.x, l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
 }
 __global__ void __launch_bounds__(256, 2)
@@ -815,6 +819,8 @@ lcol_mma_kernel(const float* __restrict__ u11, int ldu, float* __restrict__ a21,
                 float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    pdl_release();
+    pdl_wait();
     lcol_mma_body(smem_raw, blockIdx.x, u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
 }
 // Both solves of one inner block in one launch: they only depend on the diagonal factor, not on each other, and
@@ -826,6 +832,8 @@ urow_lcol_mma_kernel(const float* __restrict__ d11, int ldd, int n_ucta,
                      float* __restrict__ a21, int ld21, int nrows, float* __restrict__ la_hi, float* __restrict__ la_lo, int ldla, int k_la)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    pdl_release();
+    pdl_wait();
     if ((int)blockIdx.x < n_ucta) urow_mma_body(smem_raw, blockIdx.x, d11, ldd, a12, ld12, ncols, ub_hi, ub_lo, ldub, k_ub);
     else lcol_mma_body(smem_raw, (int)blockIdx.x - n_ucta, d11, ldd, a21, ld21, nrows, la_hi, la_lo, ldla, k_la);
 }
@@ -837,8 +845,8 @@ void launch_urow_lcol(const float* d11, int ldd,
     if (ncols > 0 && nrows > 0 && ub_hi != nullptr && la_hi != nullptr && panel_mma_enabled() && panel_fuse_enabled()) {
         const int n_ucta = (ncols + UW - 1) / UW, n_lcta = (nrows + LH - 1) / LH;
         constexpr size_t smem = sizeof(UrowMmaSmem) > sizeof(LcolMmaSmem) ? sizeof(UrowMmaSmem) : sizeof(LcolMmaSmem);
-        urow_lcol_mma_kernel<<<n_ucta + n_lcta, 256, smem, s>>>(d11, ldd, n_ucta, a12, ld12, ncols, ub_hi, ub_lo, ldub, k_ub,
-                                                                 a21, ld21, nrows, la_hi, la_lo, ldla, k_la);
+        launch_k(urow_lcol_mma_kernel, dim3(n_ucta + n_lcta), dim3(256), smem, s, d11, ldd, n_ucta, a12, ld12, ncols, ub_hi, ub_lo, ldub, k_ub,
+                 a21, ld21, nrows, la_hi, la_lo, ldla, k_la);
         ++g_launch_count;
         return;
     }
@@ -848,11 +856,11 @@ void launch_urow_lcol(const float* d11, int ldd,
 
 static void launch_urow_mma(const float* l11, int ldl, float* a12, int ld, int ncols, float* ub_hi, float* ub_lo, int ldub, int k_ub, cudaStream_t s)
 {
-    urow_mma_kernel<<<(ncols + UW - 1) / UW, 256, sizeof(UrowMmaSmem), s>>>(l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
+    launch_k(urow_mma_kernel, dim3((ncols + UW - 1) / UW), dim3(256), sizeof(UrowMmaSmem), s, l11, ldl, a12, ld, ncols, ub_hi, ub_lo, ldub, k_ub);
 }
 static void launch_lcol_mma(const float* u11, int ldu, float* a21, int ld, int nrows, float* la_hi, float* la_lo, int ldla, int k_la, cudaStream_t s)
 {
-    lcol_mma_kernel<<<(nrows + LH - 1) / LH, 256, sizeof(LcolMmaSmem), s>>>(u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
+    launch_k(lcol_mma_kernel, dim3((nrows + LH - 1) / LH), dim3(256), sizeof(LcolMmaSmem), s, u11, ldu, a21, ld, nrows, la_hi, la_lo, ldla, k_la);
 }
 
 void panel_setup_device()

@@ -14,6 +14,7 @@
 namespace gb200 {
 
 thread_local long long g_launch_count = 0;
+thread_local bool t_pdl = false;
 
 __device__ __forceinline__ float tf32_hi(float x) {
     uint32_t r;
@@ -484,6 +485,8 @@ __global__ void split_rowmajor_kernel(const float* __restrict__ src, int lds, fl
 {
     const int c4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int r = blockIdx.y;
+    pdl_release();
+    pdl_wait();
     if (c4 >= ldd || r >= rows) return;
     float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -501,6 +504,8 @@ __global__ void split_transpose_kernel(const float* __restrict__ src, int lds, f
     __shared__ float t[32][33];
     const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
     const int tx = threadIdx.x, ty = threadIdx.y;          // 32 x 8
+    pdl_release();
+    pdl_wait();
     for (int i = ty; i < 32; i += 8) {
         const int r = r0 + i, c = c0 + tx;
         t[i][tx] = (r < rows && c < cols) ? src[(size_t)r * lds + c] : 0.f;
@@ -518,14 +523,14 @@ __global__ void split_transpose_kernel(const float* __restrict__ src, int lds, f
 void launch_split_rowmajor(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, cudaStream_t s)
 {
     dim3 grid((ldd / 4 + 127) / 128, rows);
-    split_rowmajor_kernel<<<grid, 128, 0, s>>>(src, lds, hi, lo, ldd, rows, cols);
+    launch_k(split_rowmajor_kernel, grid, dim3(128), 0, s, src, lds, hi, lo, ldd, rows, cols);
     ++g_launch_count;
 }
 void launch_split_transpose(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols, int rext, cudaStream_t s)
 {
     if (cols <= 0 || rext <= 0) return;
     dim3 grid((cols + 31) / 32, (rext + 31) / 32);
-    split_transpose_kernel<<<grid, dim3(32, 8), 0, s>>>(src, lds, hi, lo, ldd, rows, cols, rext);
+    launch_k(split_transpose_kernel, grid, dim3(32, 8), 0, s, src, lds, hi, lo, ldd, rows, cols, rext);
     ++g_launch_count;
 }
 

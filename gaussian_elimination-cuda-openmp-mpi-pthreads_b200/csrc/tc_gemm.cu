@@ -191,6 +191,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
     volatile int* q_tile = reinterpret_cast<volatile int*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 13));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    pdl_release();
     const int num_n = (n + TBN - 1) / TBN;
     const int num_m = (m + TBM - 1) / TBM;
     const int num_tiles = num_m * num_n;
@@ -210,6 +211,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_constant
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 4));
+    pdl_wait();                                             // predecessors' operands / C are complete from here on
 
     if (warp == 0) {
         // ===================== TMA producer =====================
@@ -483,6 +485,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();                // 0: even CTA (issues the MMAs), 1: its peer
+    pdl_release();
     const int pair = (int)blockIdx.x >> 1, num_pairs = (int)gridDim.x >> 1;
     const int num_n = (n + TBN - 1) / TBN;
     const int num_m = (m + TBM2 - 1) / TBM2;
@@ -504,6 +507,7 @@ tc_gemm_pair_kernel(const __grid_constant__ CUtensorMap tm_ahi, const __grid_con
     cluster_sync_all();                                     // barriers of both CTAs initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(gen_base + Cfg::bar_off + 8 * (2 * STAGES + 4));
+    pdl_wait();
 
     if (warp == 0) {
         // ===================== TMA producer (both CTAs) =====================
@@ -756,7 +760,7 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
     int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
-    tc_gemm_kernel<BK, STAGES><<<grid, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched, dyn, max_tiles);
+    launch_k(tc_gemm_kernel<BK, STAGES>, dim3(grid), dim3(kTcThreads), (size_t)Cfg::smem_bytes, s, ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched, dyn, max_tiles);
     ++g_launch_count;
     return (int)cudaGetLastError();
 }
@@ -790,8 +794,8 @@ static int launch_pair(const float* Ahi, const float* Alo, int lda, const float*
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
     int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
-    tc_gemm_pair_kernel<BK, STAGES><<<2 * pairs, kTcThreads, Cfg::smem_bytes, s>>>(ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0,
-                                                                                   sched, dyn, max_tiles);
+    launch_k(tc_gemm_pair_kernel<BK, STAGES>, dim3(2 * pairs), dim3(kTcThreads), (size_t)Cfg::smem_bytes, s, ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0,
+             sched, dyn, max_tiles);
     ++g_launch_count;
     return (int)cudaGetLastError();
 }
