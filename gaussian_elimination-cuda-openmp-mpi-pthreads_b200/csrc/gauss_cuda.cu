@@ -200,6 +200,9 @@ struct gauss_cuda_ctx {
     bool p2p = false;
     float* pbox = nullptr;                      // this rank's receive box: [1024 B of flag words | pcrit[0] | pcrit[1]], pcrit = 4 x NB x NB floats
     float* peer_pbox = nullptr;                 // the next rank's box, mapped into this process
+    float* peer_box[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};   // every other rank's box (world <= 8)
+    float* iu_all = nullptr;                    // [owned blocks][NB x NB] inv(U11) of this rank's outer blocks (back substitution)
+    unsigned bs_count = 0;                      // back substitutions run by this context
     unsigned* push_counters = nullptr;          // device: completion counters of the two pushing kernels
     unsigned solve_seq = 0;                     // factorisations run by this context (every rank counts alike): flag values are seq * nblk + K + 1
     bool memops = false;                        // cuStreamWaitValue32 available (else a spinning one-warp kernel waits)
@@ -246,11 +249,11 @@ static StreamWaitValue32Fn g_wait_value32 = nullptr;
 static int p2p_setup(gauss_cuda_ctx* c)
 {
     const size_t nb2 = (size_t)c->NB * c->NB;
-    const size_t box_bytes = 1024 + 8 * nb2 * sizeof(float);
+    const size_t box_bytes = 1024 + 8 * nb2 * sizeof(float) + (size_t)c->np * sizeof(float);   // flags | pcrit[2] | solution receive vector
     CK(cudaMalloc((void**)&c->pbox, box_bytes));
     CK(cudaMemset(c->pbox, 0, box_bytes));
-    CK(cudaMalloc((void**)&c->push_counters, 64));
-    CK(cudaMemset(c->push_counters, 0, 64));
+    CK(cudaMalloc((void**)&c->push_counters, 256));
+    CK(cudaMemset(c->push_counters, 0, 256));
     if (!g_nccl.AllGather) return GAUSS_CUDA_OK;                   // old NCCL without the symbol: broadcast only
     unsigned char* stage = nullptr;
     const size_t slot = 128;
@@ -266,13 +269,16 @@ static int p2p_setup(gauss_cuda_ctx* c)
     CK(cudaMemcpy(host.data(), stage, slot * (c->world + 1), cudaMemcpyDeviceToHost));
     const char* env = getenv("GAUSS_CUDA_P2P");
     if (env && atoi(env) == 0) ok = 0;
-    if (ok) {
+    if (c->world > 8) ok = 0;
+    for (int r = 0; ok && r < c->world; ++r) {                     // every peer's box (the crit push uses the next rank's only)
+        if (r == c->rank) continue;
         cudaIpcMemHandle_t hn;
-        memcpy(&hn, host.data() + slot * (1 + (c->rank + 1) % c->world), sizeof hn);
+        memcpy(&hn, host.data() + slot * (1 + r), sizeof hn);
         void* p = nullptr;
-        if (cudaIpcOpenMemHandle(&p, hn, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess) c->peer_pbox = (float*)p;
+        if (cudaIpcOpenMemHandle(&p, hn, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess) c->peer_box[r] = (float*)p;
         else { ok = 0; cudaGetLastError(); }
     }
+    if (ok) c->peer_pbox = c->peer_box[(c->rank + 1) % c->world];
     memset(host.data(), 0, slot);
     host[0] = (unsigned char)ok;
     CK(cudaMemcpy(stage, host.data(), slot, cudaMemcpyHostToDevice));
@@ -283,6 +289,11 @@ static int p2p_setup(gauss_cuda_ctx* c)
     for (int r = 0; r < c->world; ++r) all = all && host[slot * (1 + r)] == 1;
     CK(cudaFree(stage));
     c->p2p = all;
+    if (all) {
+        int nown = 0;
+        for (int R = c->rank; R < c->nblk; R += c->world) ++nown;
+        CK(cudaMalloc((void**)&c->iu_all, (size_t)std::max(nown, 1) * nb2 * sizeof(float)));
+    }
     if (!g_wait_value32) {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult q;
@@ -505,7 +516,8 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
                              c->ev_near[0], c->ev_near[1], c->ev_nearlocal[0], c->ev_nearlocal[1], c->ev_rownear[0], c->ev_rownear[1]};
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
     }
-    if (c->peer_pbox) cudaIpcCloseMemHandle(c->peer_pbox);
+    for (float* pb : c->peer_box) if (pb) cudaIpcCloseMemHandle(pb);
+    if (c->iu_all) cudaFree(c->iu_all);
     if (c->pbox) cudaFree(c->pbox);
     if (c->push_counters) cudaFree(c->push_counters);
     if (c->status) cudaFree(c->status);
@@ -1201,7 +1213,8 @@ static int factor_cp(gauss_cuda_ctx* c)
         const bool push = p2p && K + 1 < nblk;
         float* pc = push ? box_crit(c->peer_pbox, pq(K)) : nullptr;
         launch_ext_finish(c->ext, lde, kb, A11, ld, c->il[0], c->il[1], iut_hi(b), iut_lo(b), NB,
-                          pc, pc ? pc + nb2 : nullptr, c->push_counters, push ? reinterpret_cast<unsigned*>(c->peer_pbox) : nullptr, seq_of(K), sp);
+                          pc, pc ? pc + nb2 : nullptr, c->push_counters, push ? reinterpret_cast<unsigned*>(c->peer_pbox) : nullptr, seq_of(K),
+                          c->iu_all ? c->iu_all + (size_t)(K / c->world) * nb2 : nullptr, sp);
         CK(cudaEventRecord(c->ev_inv[b], sp));
         return GAUSS_CUDA_OK;
     };
@@ -1473,6 +1486,39 @@ static int backsub(gauss_cuda_ctx* c)
     const int ld = c->ld, NB = c->NB, np = c->np;
     if (c->world == 1) {                   // one launch; U is streamed once, W stays untouched
         launch_trsv_fused(c->W, ld, np, np, c->xvec, c->trsv_ctrl, s);
+        CK(cudaGetLastError());
+        return GAUSS_CUDA_OK;
+    }
+    if (c->cp && c->p2p && c->iu_all) {
+        // peer-memory form: the owner multiplies by the stored inv(U11) and writes x_K into every rank's receive vector
+        // itself (one kernel, fused with its broadcast); the others wait on a flag word, then fold x_K into their rows
+        const size_t nb2 = (size_t)NB * NB;
+        float* xr = c->pbox + 256 + 8 * nb2;                         // this rank's receive vector (np floats)
+        c->bs_count += 1;
+        for (int K = c->nblk - 1; K >= 0; --K) {
+            const int k0 = K * NB, kb = blk_rows(c, K), owner = K % c->world;
+            const unsigned seq = c->bs_count * (unsigned)(c->nblk + 1) + (unsigned)(c->nblk - K);
+            if (owner == c->rank) {
+                BsPeers peers{};
+                for (int r = 0; r < c->world; ++r) {
+                    if (r == c->rank) continue;
+                    peers.x[peers.n] = c->peer_box[r] + 256 + 8 * nb2 + k0;
+                    peers.flag[peers.n] = reinterpret_cast<unsigned*>(c->peer_box[r]) + 64;
+                    ++peers.n;
+                }
+                const float* P = c->W + (size_t)blk_local_row(c, K) * ld;
+                launch_bs_solve_push(c->iu_all + (size_t)(K / c->world) * nb2, NB, P + np, ld, kb, xr + k0, peers, c->push_counters + 16, seq, s);
+            } else {
+                const unsigned* f = reinterpret_cast<const unsigned*>(c->pbox) + 64;
+                if (c->memops) {
+                    if (g_wait_value32(s, (unsigned long long)(uintptr_t)f, seq, 0x0) != 0) { snprintf(g_err, sizeof g_err, "cuStreamWaitValue32 failed"); return GAUSS_CUDA_CUDA_ERR; }
+                } else launch_wait_flag(f, seq, s);
+                c->bcast_bytes += (double)kb * sizeof(float);
+            }
+            const int mabove = local_blocks_before(c, K) * NB;
+            launch_trsv_gemv_wide(c->W + k0, ld, np - k0, xr + k0, mabove, kb, s);
+        }
+        CK(cudaMemcpyAsync(c->xvec, xr, (size_t)np * sizeof(float), cudaMemcpyDeviceToDevice, s));
         CK(cudaGetLastError());
         return GAUSS_CUDA_OK;
     }

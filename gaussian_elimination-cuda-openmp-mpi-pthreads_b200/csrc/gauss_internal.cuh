@@ -75,7 +75,11 @@ void launch_ext_prepare(const float* a11, int ld, float* E, int lde, int kb, cud
 // memory set to `seq` once every CTA's stores are out; counter: one zeroed device word per launch site.
 void launch_ext_finish(const float* E, int lde, int kb, float* a11, int ld,
                        float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo,
-                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s);
+                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, float* iu_raw, cudaStream_t s);
+// x_K = inv(U11) y_K on the owner, stored locally and into every peer's receive vector, then the peers' flags
+struct BsPeers { float* x[8]; unsigned* flag[8]; int n; };
+void launch_bs_solve_push(const float* iu, int ldiu, const float* ycol, int ld, int kb, float* x_local, const BsPeers& peers,
+                          unsigned* counter, unsigned seq, cudaStream_t s);
 // hi/lo split of a row-major block into local (and peer) operand buffers, then the peer's flag
 void launch_crit_split(const float* src, int lds, float* hi, float* lo, int ldd, int rows, int cols,
                        float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s);

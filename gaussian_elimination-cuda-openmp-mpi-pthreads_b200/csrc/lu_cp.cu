@@ -86,7 +86,8 @@ void launch_ext_prepare(const float* a11, int ld, float* E, int lde, int kb, cud
 __global__ void __launch_bounds__(256)
 ext_finish_kernel(const float* __restrict__ E, int lde, int kb, float* __restrict__ a11, int ld,
                   float* __restrict__ il_hi, float* __restrict__ il_lo, float* __restrict__ iut_hi, float* __restrict__ iut_lo, int ldo,
-                  float* __restrict__ peer_hi, float* __restrict__ peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq)
+                  float* __restrict__ peer_hi, float* __restrict__ peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq,
+                  float* __restrict__ iu_raw)
 {
     __shared__ float t[32][33];
     const int tx = threadIdx.x, ty = threadIdx.y;
@@ -106,7 +107,11 @@ ext_finish_kernel(const float* __restrict__ E, int lde, int kb, float* __restric
         }
     } else {
         const int r0 = (blockIdx.y - nby) * 32;                  // row block of inv(U11)
-        for (int i = ty; i < 32; i += 8) t[i][tx] = E[(size_t)(kb + r0 + i) * lde + c0 + tx];
+        for (int i = ty; i < 32; i += 8) {
+            const float v = E[(size_t)(kb + r0 + i) * lde + c0 + tx];
+            t[i][tx] = v;
+            if (iu_raw != nullptr) iu_raw[(size_t)(r0 + i) * ldo + c0 + tx] = v;     // inv(U11) itself, kept for back substitution
+        }
         __syncthreads();
         for (int i = ty; i < 32; i += 8) {
             float h, l;
@@ -124,10 +129,10 @@ ext_finish_kernel(const float* __restrict__ E, int lde, int kb, float* __restric
 
 void launch_ext_finish(const float* E, int lde, int kb, float* a11, int ld,
                        float* il_hi, float* il_lo, float* iut_hi, float* iut_lo, int ldo,
-                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, cudaStream_t s)
+                       float* peer_hi, float* peer_lo, unsigned* counter, unsigned* peer_flag, unsigned seq, float* iu_raw, cudaStream_t s)
 {
     dim3 grid(kb / 32, 2 * (kb / 32));
-    launch_k(ext_finish_kernel, grid, dim3(32, 8), 0, s, E, lde, kb, a11, ld, il_hi, il_lo, iut_hi, iut_lo, ldo, peer_hi, peer_lo, counter, peer_flag, seq);
+    launch_k(ext_finish_kernel, grid, dim3(32, 8), 0, s, E, lde, kb, a11, ld, il_hi, il_lo, iut_hi, iut_lo, ldo, peer_hi, peer_lo, counter, peer_flag, seq, iu_raw);
     ++g_launch_count;
 }
 
@@ -160,6 +165,54 @@ void launch_crit_split(const float* src, int lds, float* hi, float* lo, int ldd,
 {
     dim3 grid((cols / 4 + 127) / 128, rows);
     launch_k(crit_split_kernel, grid, dim3(128), 0, s, src, lds, hi, lo, ldd, rows, cols, peer_hi, peer_lo, counter, peer_flag, seq);
+    ++g_launch_count;
+}
+
+// Back substitution step of one outer block on its owner, fused with its broadcast (solveGauss,
+// gauss_internal_input.c:144-159, for the rows of the block):  x_K = inv(U11) * y_K  as a matrix-vector product (a warp
+// per row; y_K is the right-hand-side column of the block's rows, already reduced by the blocks solved before), stored
+// into the owner's solution vector and straight into every peer's receive vector over NVLink; the last CTA then sets
+// every peer's flag word.  Replaces, per outer block, a chained triangular solve plus one NCCL broadcast.
+__global__ void __launch_bounds__(256)
+bs_solve_push_kernel(const float* __restrict__ iu, int ldiu, const float* __restrict__ ycol, int ld, int kb,
+                     float* __restrict__ x_local, BsPeers peers, unsigned* counter, unsigned seq)
+{
+    extern __shared__ float ysm[];
+    for (int j = threadIdx.x; j < kb; j += blockDim.x) ysm[j] = ycol[(size_t)j * ld];
+    __syncthreads();
+    const int lane = threadIdx.x & 31, row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row < kb) {
+        float acc = 0.f;
+        const int j0 = (row / 128) * 128;                         // inv(U11) is upper triangular: columns left of the row's 128-block are zero
+        for (int j = j0 + 4 * lane; j < kb; j += 128) {
+            const float4 a = *reinterpret_cast<const float4*>(iu + (size_t)row * ldiu + j);
+            acc = fmaf(a.x, ysm[j], acc); acc = fmaf(a.y, ysm[j + 1], acc); acc = fmaf(a.z, ysm[j + 2], acc); acc = fmaf(a.w, ysm[j + 3], acc);
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+        if (lane == 0) {
+            x_local[row] = acc;
+            for (int p = 0; p < peers.n; ++p) peers.x[p][row] = acc;
+        }
+    }
+    if (peers.n > 0) {
+        __threadfence_system();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence_system();
+            if (atomicAdd(counter, 1u) == gridDim.x - 1) {
+                *counter = 0;
+                __threadfence_system();
+                for (int p = 0; p < peers.n; ++p)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(peers.flag[p]), "r"(seq) : "memory");
+            }
+        }
+    }
+}
+void launch_bs_solve_push(const float* iu, int ldiu, const float* ycol, int ld, int kb, float* x_local, const BsPeers& peers,
+                          unsigned* counter, unsigned seq, cudaStream_t s)
+{
+    bs_solve_push_kernel<<<(kb + 7) / 8, 256, kb * sizeof(float), s>>>(iu, ldiu, ycol, ld, kb, x_local, peers, counter, seq);
     ++g_launch_count;
 }
 
