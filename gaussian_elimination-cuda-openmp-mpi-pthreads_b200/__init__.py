@@ -248,12 +248,17 @@ class GaussCuda:
     constructing this object; gauss() = computeGauss + solveGauss.
     """
 
-    def __init__(self, nsize, nb=0, mode=MODE_3XTF32, rank=0, world=1, device=None, nccl_id=None):
+    def __init__(self, nsize, nb=0, mode=MODE_3XTF32, rank=0, world=1, device=None, nccl_id=None, ngpus=1):
+        """ngpus > 1: ONE process drives GPUs 0..ngpus-1 (gauss_cuda_init's single-process group); rank/world/device/nccl_id
+        describe one rank of the one-process-per-GPU form (gauss_cuda_init_dist)."""
         self._h = C.c_void_p()
         self.n = int(nsize)
         self.rank, self.world = rank, world
         L = lib()
-        if world == 1 and device is None:
+        if ngpus > 1:
+            self.world = ngpus
+            _check(L.gauss_cuda_init(C.byref(self._h), self.n, ngpus, nb, mode))
+        elif world == 1 and device is None:
             _check(L.gauss_cuda_init(C.byref(self._h), self.n, 1, nb, mode))
         else:
             idbuf = C.create_string_buffer(bytes(nccl_id), 128) if nccl_id is not None else None

@@ -26,7 +26,10 @@
 #include <string.h>
 #include <math.h>
 #include <algorithm>
+#include <string>
+#include <functional>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 using namespace gb200;
@@ -225,7 +228,29 @@ struct gauss_cuda_ctx {
     bool resident = false, factored = false;
     double bcast_bytes = 0.0;
     gauss_cuda_stats last{};
+    // single-process group (gauss_cuda_init with ngpus > 1): this object is only a handle; members[r] is the context of
+    // rank r on device r, each driven by its own host thread during a call
+    std::vector<gauss_cuda_ctx*> members;
+    bool in_group = false;                      // a member: peers are reached by direct peer access, not CUDA IPC
+    std::vector<float> group_tmp;               // host scratch for the X / B_out of ranks > 0
 };
+
+// Runs `fn(member, rank)` for every member of a group, one host thread per rank (rank 0 on the caller's), and returns
+// the first failing status; the failing thread's message becomes the caller's gauss_cuda_last_error().
+static int group_call(gauss_cuda_ctx* g, const std::function<int(gauss_cuda_ctx*, int)>& fn)
+{
+    const int n = (int)g->members.size();
+    std::vector<int> rc((size_t)n, GAUSS_CUDA_OK);
+    std::vector<std::string> msg((size_t)n);
+    std::vector<std::thread> th;
+    for (int r = 1; r < n; ++r)
+        th.emplace_back([&, r] { rc[r] = fn(g->members[r], r); if (rc[r]) msg[r] = g_err; });
+    rc[0] = fn(g->members[0], 0);
+    for (auto& t : th) t.join();
+    for (int r = 0; r < n; ++r)
+        if (rc[r]) { if (r) snprintf(g_err, sizeof g_err, "rank %d: %s", r, msg[r].c_str()); return rc[r]; }
+    return GAUSS_CUDA_OK;
+}
 
 static inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
@@ -305,7 +330,7 @@ static int p2p_setup(gauss_cuda_ctx* c)
     return GAUSS_CUDA_OK;
 }
 
-static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int device, const void* nccl_id, int nb, int mode)
+static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int device, const void* nccl_id, int nb, int mode, bool in_group = false)
 {
     if (!out) return GAUSS_CUDA_BAD_ARG;
     *out = nullptr;
@@ -322,7 +347,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         return GAUSS_CUDA_CUDA_ERR;
     }
     gauss_cuda_ctx* c = new gauss_cuda_ctx();
-    c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode;
+    c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode; c->in_group = in_group;
     { const char* g = getenv("GAUSS_CUDA_GRAPH"); if (g && atoi(g) == 0) c->use_graph = false; }
     {   // single-GPU look-ahead (GAUSS_CUDA_OVERLAP=1): measured on B200 it is a wash -- the urow/lcol kernels are
         // throughput-bound, so running them beside the bulk update only moves SM time around (N=32768: 132.0 ms
@@ -468,16 +493,86 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         memcpy(&id, nccl_id, sizeof id);
         ncclResult_t r = g_nccl.CommInitRank(&c->comm, world, id, rank);
         if (r != ncclSuccess) { rc = nccl_fail(r, "ncclCommInitRank", __LINE__); gauss_cuda_free(c); return rc; }
-        if (c->cp && (rc = p2p_setup(c))) { gauss_cuda_free(c); return rc; }
+        if (c->cp && !c->in_group && (rc = p2p_setup(c))) { gauss_cuda_free(c); return rc; }
     }
     *out = c;
     return GAUSS_CUDA_OK;
 }
 
+// Peer wiring of a single-process group: every member gets its receive box and direct pointers to the others' (peer
+// access between the devices enabled both ways); any failure leaves the whole group on the broadcast-only path.
+static int group_p2p_setup(gauss_cuda_ctx* g)
+{
+    const int n = (int)g->members.size();
+    bool ok = n <= 8 && !(getenv("GAUSS_CUDA_P2P") && atoi(getenv("GAUSS_CUDA_P2P")) == 0);
+    for (int r = 0; r < n && ok; ++r) ok = g->members[r]->cp;
+    if (!ok) return GAUSS_CUDA_OK;
+    for (int r = 0; r < n; ++r) {
+        gauss_cuda_ctx* c = g->members[r];
+        CK(cudaSetDevice(c->device));
+        const size_t nb2 = (size_t)c->NB * c->NB;
+        const size_t box_bytes = 1024 + 8 * nb2 * sizeof(float) + (size_t)c->np * sizeof(float);
+        CK(cudaMalloc((void**)&c->pbox, box_bytes));
+        CK(cudaMemset(c->pbox, 0, box_bytes));
+        CK(cudaMalloc((void**)&c->push_counters, 256));
+        CK(cudaMemset(c->push_counters, 0, 256));
+        for (int q = 0; q < n && ok; ++q) {
+            if (q == r) continue;
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, c->device, g->members[q]->device) != cudaSuccess || !can) { ok = false; break; }
+            cudaError_t e = cudaDeviceEnablePeerAccess(g->members[q]->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = false;
+            cudaGetLastError();
+        }
+    }
+    if (!ok) return GAUSS_CUDA_OK;
+    for (int r = 0; r < n; ++r) {
+        gauss_cuda_ctx* c = g->members[r];
+        CK(cudaSetDevice(c->device));
+        for (int q = 0; q < n; ++q) if (q != r) c->peer_box[q] = g->members[q]->pbox;
+        c->peer_pbox = c->peer_box[(r + 1) % n];
+        int nown = 0;
+        for (int R = c->rank; R < c->nblk; R += c->world) ++nown;
+        CK(cudaMalloc((void**)&c->iu_all, (size_t)std::max(nown, 1) * c->NB * c->NB * sizeof(float)));
+        if (!g_wait_value32) {
+            void* fn = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &q) == cudaSuccess && fn) g_wait_value32 = (StreamWaitValue32Fn)fn;
+            cudaGetLastError();
+        }
+        const char* mo = getenv("GAUSS_CUDA_MEMOPS");
+        c->memops = g_wait_value32 != nullptr && !(mo && atoi(mo) == 0);
+        c->p2p = true;
+    }
+    return GAUSS_CUDA_OK;
+}
+
 extern "C" int gauss_cuda_init(gauss_cuda_ctx** ctx, int n, int ngpus, int nb, int mode)
 {
+    if (ngpus > 1) {
+        // one process, ngpus devices (0 .. ngpus-1): one rank context per device, each call runs them on their own host
+        // threads -- the reference's own multi-worker form is one program too (mpirun ... gauss_internal_input, README.txt:23)
+        if (!ctx) return GAUSS_CUDA_BAD_ARG;
+        *ctx = nullptr;
+        if (gauss_cuda_device_count() < ngpus) {
+            snprintf(g_err, sizeof g_err, "gauss_cuda_init: %d GPUs asked for, %d visible (no CPU fallback)", ngpus, gauss_cuda_device_count());
+            return GAUSS_CUDA_CUDA_ERR;
+        }
+        char id[128];
+        int rc = gauss_cuda_unique_id(id);
+        if (rc) return rc;
+        gauss_cuda_ctx* g = new gauss_cuda_ctx();
+        g->n = n; g->world = ngpus; g->mode = mode;
+        g->members.assign((size_t)ngpus, nullptr);
+        rc = group_call(g, [&](gauss_cuda_ctx*, int r) { return ctx_create(&g->members[r], n, r, ngpus, r, id, nb, mode, true); });
+        if (rc == GAUSS_CUDA_OK) rc = group_p2p_setup(g);
+        if (rc) { gauss_cuda_free(g); return rc; }
+        g->group_tmp.assign(2 * (size_t)n * (size_t)ngpus, 0.f);
+        *ctx = g;
+        return GAUSS_CUDA_OK;
+    }
     if (ngpus != 1) {
-        snprintf(g_err, sizeof g_err, "gauss_cuda_init drives one GPU per process; use gauss_cuda_init_dist for %d", ngpus);
+        snprintf(g_err, sizeof g_err, "gauss_cuda_init: ngpus must be >= 1 (got %d)", ngpus);
         return GAUSS_CUDA_BAD_ARG;
     }
     int dev = 0;
@@ -495,6 +590,13 @@ extern "C" int gauss_cuda_init_dist(gauss_cuda_ctx** ctx, int n, int rank, int w
 extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
 {
     if (!c) return;
+    if (!c->members.empty()) {                                   // a group handle: NCCL teardown wants every rank, so in threads
+        std::vector<std::thread> th;
+        for (gauss_cuda_ctx* m : c->members) if (m) th.emplace_back([m] { gauss_cuda_free(m); });
+        for (auto& t : th) t.join();
+        delete c;
+        return;
+    }
     cudaSetDevice(c->device);
     if (c->s_main) cudaStreamSynchronize(c->s_main);
     if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
@@ -516,7 +618,7 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
                              c->ev_near[0], c->ev_near[1], c->ev_nearlocal[0], c->ev_nearlocal[1], c->ev_rownear[0], c->ev_rownear[1]};
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
     }
-    for (float* pb : c->peer_box) if (pb) cudaIpcCloseMemHandle(pb);
+    if (!c->in_group) for (float* pb : c->peer_box) if (pb) cudaIpcCloseMemHandle(pb);
     if (c->iu_all) cudaFree(c->iu_all);
     if (c->pbox) cudaFree(c->pbox);
     if (c->push_counters) cudaFree(c->push_counters);
@@ -1717,6 +1819,13 @@ static int stream_setup(gauss_cuda_ctx* c)
 extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* B, float* X, float* B_out, gauss_cuda_stats* st)
 {
     if (!c || !A || !B || !X) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) {
+        const size_t n = (size_t)c->n;
+        return group_call(c, [&](gauss_cuda_ctx* m, int r) {
+            float* tx = c->group_tmp.data() + 2 * n * (size_t)r;
+            return gauss_cuda_solve(m, A, B, r ? tx : X, B_out ? (r ? tx + n : B_out) : nullptr, r ? nullptr : st);
+        });
+    }
     CK(cudaSetDevice(c->device));
     g_launch_count = 0;
     cudaStream_t s = c->s_main;
@@ -1746,6 +1855,7 @@ extern "C" int gauss_cuda_solve(gauss_cuda_ctx* c, const float* A, const float* 
 extern "C" int gauss_cuda_upload(gauss_cuda_ctx* c, const float* A, const float* B)
 {
     if (!c || !A || !B) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) return group_call(c, [&](gauss_cuda_ctx* m, int) { return gauss_cuda_upload(m, A, B); });
     CK(cudaSetDevice(c->device));
     if (!c->W0) CK(cudaMalloc((void**)&c->W0, (size_t)std::max(c->rows_local, 1) * c->ld * sizeof(float)));
     int rc = upload_into(c, c->W0, A, B);
@@ -1761,6 +1871,7 @@ extern "C" int gauss_cuda_upload(gauss_cuda_ctx* c, const float* A, const float*
 extern "C" int gauss_cuda_init_matrix_device(gauss_cuda_ctx* c)
 {
     if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) return group_call(c, [&](gauss_cuda_ctx* m, int) { return gauss_cuda_init_matrix_device(m); });
     CK(cudaSetDevice(c->device));
     if (!c->W0) CK(cudaMalloc((void**)&c->W0, (size_t)std::max(c->rows_local, 1) * c->ld * sizeof(float)));
     cudaStream_t s = c->s_main;
@@ -1788,6 +1899,7 @@ static int restore_working(gauss_cuda_ctx* c)
 extern "C" int gauss_cuda_solve_resident(gauss_cuda_ctx* c, gauss_cuda_stats* st)
 {
     if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) return group_call(c, [&](gauss_cuda_ctx* m, int r) { return gauss_cuda_solve_resident(m, r ? nullptr : st); });
     if (!c->resident) return GAUSS_CUDA_NOT_READY;
     CK(cudaSetDevice(c->device));
     g_launch_count = 0;
@@ -1803,6 +1915,7 @@ extern "C" int gauss_cuda_solve_resident(gauss_cuda_ctx* c, gauss_cuda_stats* st
 extern "C" int gauss_cuda_compute_gauss(gauss_cuda_ctx* c, gauss_cuda_stats* st)
 {
     if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) return group_call(c, [&](gauss_cuda_ctx* m, int r) { return gauss_cuda_compute_gauss(m, r ? nullptr : st); });
     if (!c->resident) return GAUSS_CUDA_NOT_READY;
     CK(cudaSetDevice(c->device));
     g_launch_count = 0;
@@ -1822,6 +1935,7 @@ extern "C" int gauss_cuda_compute_gauss(gauss_cuda_ctx* c, gauss_cuda_stats* st)
 extern "C" int gauss_cuda_solve_gauss(gauss_cuda_ctx* c, gauss_cuda_stats* st)
 {
     if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) return group_call(c, [&](gauss_cuda_ctx* m, int r) { return gauss_cuda_solve_gauss(m, r ? nullptr : st); });
     if (!c->resident || !c->factored) return GAUSS_CUDA_NOT_READY;
     CK(cudaSetDevice(c->device));
     g_launch_count = 0;
@@ -1837,6 +1951,13 @@ extern "C" int gauss_cuda_solve_gauss(gauss_cuda_ctx* c, gauss_cuda_stats* st)
 extern "C" int gauss_cuda_download(gauss_cuda_ctx* c, float* X, float* B_out)
 {
     if (!c) return GAUSS_CUDA_BAD_ARG;
+    if (!c->members.empty()) {
+        const size_t n = (size_t)c->n;
+        return group_call(c, [&](gauss_cuda_ctx* m, int r) {
+            float* tx = c->group_tmp.data() + 2 * n * (size_t)r;
+            return gauss_cuda_download(m, X ? (r ? tx : X) : nullptr, B_out ? (r ? tx + n : B_out) : nullptr);
+        });
+    }
     CK(cudaSetDevice(c->device));
     int rc = download_results(c, X, B_out);
     if (rc) return rc;
@@ -1850,7 +1971,7 @@ extern "C" int gauss_cuda_solve_refined(gauss_cuda_ctx* c, const double* A, cons
                                         int max_iters, double tol, gauss_cuda_refine_info* info)
 {
     if (!c || !A || !B || !X || max_iters < 0) return GAUSS_CUDA_BAD_ARG;
-    if (c->world != 1) {
+    if (c->world != 1 || !c->members.empty()) {
         snprintf(g_err, sizeof g_err, "gauss_cuda_solve_refined: single-GPU contexts only");
         return GAUSS_CUDA_BAD_ARG;
     }

@@ -27,6 +27,7 @@ static gauss_cuda_ctx *ctx;
 static gauss_cuda_stats stats;
 static int g_mode = GAUSS_CUDA_MODE_3XTF32;
 static int g_refine = 0;          /* -r: double-precision answers through gauss_cuda_solve_refined */
+static int g_ngpus = 1;           /* -g G: G GPUs of this node driven by this one process (block-cyclic row panels, gauss_mpi :140-155) */
 static int g_devinit = 0;         /* -d: initMatrix generated on the GPU (fixture only): no host fill, no upload */
 static gauss_cuda_refine_info rinfo;
 
@@ -49,7 +50,7 @@ void allocate_memory(int size)
     B32 = malloc(n * sizeof *B32); X32 = malloc(n * sizeof *X32); Bafter32 = malloc(n * sizeof *Bafter32);
     if (!flat || !matrix || !B || !V || !C || !swap || !A32 || !B32 || !X32 || !Bafter32) { fprintf(stderr, "out of memory\n"); exit(2); }
     for (size_t r = 0; r < n; ++r) matrix[r] = flat + r * n;
-    die_on(gauss_cuda_init(&ctx, size, 1, 0, g_mode), "gauss_cuda_init");
+    die_on(gauss_cuda_init(&ctx, size, g_ngpus, 0, g_mode), "gauss_cuda_init");
 }
 
 void initMatrix(int nsize)
@@ -108,18 +109,19 @@ void gauss(int nsize)
 
 static void usage(const char *p)
 {
-    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v] [-r] [-d]   (reference form)\n"
+    printf("Usage: %s -s <matrix size> [-t <threads, ignored>] [-m 0|1] [-v] [-r] [-d] [-g <GPUs>]   (reference form)\n"
            "       %s N [seed]                                               (seeded form)\n"
            "  -m 0 = tcgen05 3xTF32 (default), 1 = FFMA;  -v prints B[i] C[i] like VERIFY;\n"
            "  -r = double-precision answers (FP32 elimination + iterative refinement)\n"
-           "  -d = initMatrix on the GPU (no host fill, no upload; fixture form only)\n", p, p);
+           "  -d = initMatrix on the GPU (no host fill, no upload; fixture form only)\n"
+           "  -g G = use G GPUs of this node from this one process (the reference's multi-worker run is one program too)\n", p, p);
 }
 
 int main(int argc, char *argv[])
 {
     int nsize = 2048, verify = 0, seeded = 0, opt;
     unsigned seed = 1;
-    while ((opt = getopt(argc, argv, "hs:t:m:vrd")) != -1) {
+    while ((opt = getopt(argc, argv, "hs:t:m:vrdg:")) != -1) {
         switch (opt) {
             case 's': { int s = atoi(optarg); if (s > 0) nsize = s; else fprintf(stderr, "Entered size is negative, hence using the default (%d)\n", 2048); } break;
             case 't': if (atoi(optarg) <= 0) { fprintf(stderr, "Error: Threads count should be a natural number. \n"); return 0; } break;
@@ -127,6 +129,7 @@ int main(int argc, char *argv[])
             case 'v': verify = 1; break;
             case 'r': g_refine = 1; break;
             case 'd': g_devinit = 1; break;
+            case 'g': g_ngpus = atoi(optarg); if (g_ngpus < 1) { fprintf(stderr, "Error: GPU count should be a natural number. \n"); return 0; } break;
             case 'h': usage(argv[0]); return 0;
             default:  usage(argv[0]); return 1;
         }
@@ -138,6 +141,7 @@ int main(int argc, char *argv[])
         if (optind + 1 < argc) seed = (unsigned)strtoul(argv[optind + 1], NULL, 10);
     }
 
+    if (g_ngpus > 1 && g_refine) { fprintf(stderr, "-r (double-precision refinement) is a single-GPU path\n"); return 1; }
     if (g_devinit && (seeded || g_refine)) { fprintf(stderr, "-d applies to the built-in fixture in FP32 only\n"); return 1; }
     printf("\nMatrix Size: %d ; Threads: %d\n", nsize, 1);
     allocate_memory(nsize);

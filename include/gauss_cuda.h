@@ -70,9 +70,12 @@ typedef struct {
 /* ---- Gaussian elimination ------------------------------------------------------------- */
 
 /* Replaces allocate_memory(size) (gauss_internal_input.c:20-43) for the device side.
- * n: matrix order (any n >= 1); ngpus: GPUs driven by THIS process (1; the multi-GPU form
- * is one process per GPU, gauss_cuda_init_dist); nb: outer block, 0 = auto, else a
- * multiple of 128; mode: GAUSS_CUDA_MODE_*. */
+ * n: matrix order (any n >= 1); ngpus: GPUs driven by THIS process: 1, or G > 1 for devices 0..G-1 of this node
+ * (the reference's multi-worker run is one program as well: mpirun ... gauss_internal_input, OpenMP_and_MPI/README.txt:23;
+ * rows are owned block-cyclically as in gauss_cuda_init_dist, each device is driven by a host thread of the library
+ * during a call, the devices exchange panels over NVLink through NCCL and direct peer access; the context is used
+ * exactly like a single-GPU one by the calling thread; pivoting, refinement and factor download stay single-GPU);
+ * nb: outer block, 0 = auto, else a multiple of 128; mode: GAUSS_CUDA_MODE_*. */
 int gauss_cuda_init(gauss_cuda_ctx **ctx, int n, int ngpus, int nb, int mode);
 
 /* Multi-GPU form, one process per GPU: the reference's MPI row distribution

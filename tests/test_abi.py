@@ -43,7 +43,10 @@ def test_bad_arguments_rejected():
     assert L.gauss_cuda_init(C.byref(h), 0, 1, 0, 0) == pkg.BAD_ARG
     assert L.gauss_cuda_init(C.byref(h), 16, 1, 100, 0) == pkg.BAD_ARG      # nb not a multiple of 128
     assert L.gauss_cuda_init(C.byref(h), 16, 1, 0, 7) == pkg.BAD_ARG        # unknown mode
-    assert L.gauss_cuda_init(C.byref(h), 16, 2, 0, 0) == pkg.BAD_ARG        # one GPU per process
+    assert L.gauss_cuda_init(C.byref(h), 16, 0, 0, 0) == pkg.BAD_ARG        # ngpus must be >= 1
+    if pkg.device_count() < 2:                                              # a group of 2 needs 2 visible GPUs: loud failure, no fallback
+        assert L.gauss_cuda_init(C.byref(h), 16, 2, 0, 0) == pkg.CUDA_ERR
+        assert b"GPUs asked for" in L.gauss_cuda_last_error()
     assert L.gauss_cuda_solve(None, None, None, None, None, None) == pkg.BAD_ARG
     assert L.matmul_cuda(None, None, None, 4, 0, None) == pkg.BAD_ARG
     L.gauss_cuda_free(None)

@@ -72,3 +72,47 @@ def test_ranks_match_oracle(tmp_path, n, nb, mode, world):
         A, B, _ = pkg.initialize_inputs(n, 6)
         X1 = g1.gauss(A, B)
     assert np.max(np.abs(X1 - xs[0]) / np.abs(X1)) <= 1e-3
+
+
+@pytest.mark.skipif(pkg.device_count() < 2, reason="needs 2 GPUs")
+@pytest.mark.parametrize("ngpus", _worlds())
+@pytest.mark.parametrize("mode", [pkg.MODE_FFMA, pkg.MODE_3XTF32])
+@pytest.mark.parametrize("n", [2048, 700])
+def test_single_process_group_matches_oracle(n, mode, ngpus):
+    # gauss_cuda_init(ctx, n, ngpus > 1, ...): ONE process, one host thread of the caller, G devices (the reference's
+    # multi-worker run is one program too, OpenMP_and_MPI/README.txt:23).  Same tolerance as the one-process-per-GPU form.
+    import oracle_lib as ol
+    A, B, Xtrue = pkg.initialize_inputs(n, 9)
+    with pkg.GaussCuda(n, mode=mode, ngpus=ngpus) as g:
+        X, Bafter = g.gauss(A, B, want_b_after=True)
+        assert g.stats.world == ngpus
+        g.upload(A, B)
+        g.solve_resident()
+        X2 = g.download()
+        g.upload(A, B)
+        g.computeGauss()
+        g.solveGauss()
+        X3 = g.download()
+    Xref, Bref, _ = ol.gauss(A, B, nthreads=4)
+    assert ol.max_rel_error(X, Xref) <= 1e-3 and ol.max_rel_error(Bafter, Bref) <= 1e-3
+    assert ol.scaled_residual(A, B, X) <= 10.0
+    assert np.array_equal(X, X2) and np.array_equal(X, X3)
+
+
+@pytest.mark.skipif(pkg.device_count() < 2, reason="needs 2 GPUs")
+def test_harness_drives_two_gpus_from_one_process():
+    # harness/gauss_main -s N -g 2 -v : the reference program's output (gauss_internal_input.c:45-48, :225-228) from 2 GPUs
+    import re
+    import subprocess
+    exe = os.path.join(os.path.dirname(HERE), "harness", "gauss_main")
+    if not os.path.exists(exe):
+        pytest.skip("harness not built")
+    n = 4096
+    out = subprocess.run([exe, "-s", str(n), "-g", "2", "-v"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, (out.stdout[-500:], out.stderr)
+    rows = [l.split() for l in out.stdout.splitlines() if re.match(r"^-?\d+\.\d{5} -?\d+\.\d{5}$", l.strip())]
+    assert len(rows) == n
+    assert rows[0] == ["0.00000", "-0.50000"] and rows[-1] == ["0.50000", "0.50000"]
+    assert all(r == ["0.50000", "0.00000"] for r in rows[1:-1])
+    out = subprocess.run([exe, "-g", "2", "3000", "5"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, (out.stdout[-500:], out.stderr)
