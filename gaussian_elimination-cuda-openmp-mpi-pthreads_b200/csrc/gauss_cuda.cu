@@ -27,6 +27,7 @@
 #include <math.h>
 #include <algorithm>
 #include <string>
+#include <chrono>
 #include <functional>
 #include <mutex>
 #include <thread>
@@ -211,7 +212,9 @@ struct gauss_cuda_ctx {
     bool memops = false;                        // cuStreamWaitValue32 available (else a spinning one-warp kernel waits)
     int cp_near = 3;                            // outer blocks after the crit block whose U12^T travels (and is applied) ahead of the rest (GAUSS_CUDA_CP_NEAR)
     cudaEvent_t ev_near[2] = {nullptr, nullptr}, ev_nearlocal[2] = {nullptr, nullptr}, ev_rownear[2] = {nullptr, nullptr};
+    bool pdl_single = false;                    // GAUSS_CUDA_PDL_SINGLE=1: the same along the single-GPU panel chain
     bool pdl = true;                            // GAUSS_CUDA_PDL=0: the chain's kernels are launched without programmatic dependent launch
+    double host_issue_ms = 0.0;                 // host time spent issuing the last factorisation (trace)
     bool cp_nobulk = false;                     // GAUSS_CUDA_CP_NOBULK=1: timing diagnostic only (WRONG results): the bulk update is skipped
     float* ext = nullptr;                       // [2NB x 2NB] extended scratch E
     float* ext_la[2] = {nullptr, nullptr};      // hi/lo [2NB x NB]  split L of the chain inside E
@@ -349,6 +352,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     gauss_cuda_ctx* c = new gauss_cuda_ctx();
     c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode; c->in_group = in_group;
     { const char* g = getenv("GAUSS_CUDA_GRAPH"); if (g && atoi(g) == 0) c->use_graph = false; }
+    { const char* g = getenv("GAUSS_CUDA_PDL_SINGLE"); c->pdl_single = g ? atoi(g) != 0 : false; }
     {   // single-GPU look-ahead (GAUSS_CUDA_OVERLAP=1): measured on B200 it is a wash -- the urow/lcol kernels are
         // throughput-bound, so running them beside the bulk update only moves SM time around (N=32768: 132.0 ms
         // with, 128.7 ms without) -- and it is therefore off unless asked for
@@ -879,6 +883,7 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const S
 static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* ubl)
 {
     cudaStream_t s = c->s_main, ss = c->s_side, sw = c->s_wide;
+    PdlScope pdl_on(c->pdl_single);                             // the panel chain's kernels release their successors early
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     float* lah = c->la_hi[0]; float* lal = c->la_lo[0];
@@ -1570,10 +1575,12 @@ static int factor(gauss_cuda_ctx* c)
     CK(cudaMemsetAsync(c->status, 0, sizeof(int), c->s_main));
     c->bcast_bytes = 0.0;
     c->upd_count = 0;
+    const auto host_t0 = std::chrono::steady_clock::now();
     int rc = c->pivot ? factor_pivot(c)
            : c->cp ? factor_cp(c)
            : c->world > 1 ? factor_lookahead(c)
            : (c->overlap && c->nblk >= 3) ? factor_overlap(c) : factor_single(c);
+    c->host_issue_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
     if (rc) return rc;
     CK(cudaGetLastError());
     c->factored = true;
@@ -1694,8 +1701,8 @@ static int finish_stats(gauss_cuda_ctx* c, gauss_cuda_stats* st, bool h2d, bool 
         }
         cudaGetLastError();
         fprintf(stderr, "[gauss_cuda trace cp] rank %d/%d nb %d: side L21 %.2f ms, col strip %.2f | panel chain %.2f (%d panels), crit U %.2f, hand-over %.2f | "
-                        "crit-to-crit %.2f | main: wait U12 %.2f, split+row strip %.2f, bulk %.2f (factor %.2f ms)\n",
-                c->rank, c->world, c->NB, a_p2, a_cs, a_chain, n_chain, a_cu, a_hand, a_crit2crit, a_utwait, a_split, a_bulk, o.factor_s * 1e3);
+                        "crit-to-crit %.2f | main: wait U12 %.2f, split+row strip %.2f, bulk %.2f (factor %.2f ms, host issue %.2f ms)\n",
+                c->rank, c->world, c->NB, a_p2, a_cs, a_chain, n_chain, a_cu, a_hand, a_crit2crit, a_utwait, a_split, a_bulk, o.factor_s * 1e3, c->host_issue_ms);
     } else if (c->trace && fac) {
         // where the main stream's time went: [0->1] waiting for the U12 broadcast, [1->2] rebuilding the split,
         // [2->3] row strip, [3->4] column strip, [4->5] bulk update, [5->next 0] waiting for P2 of the next panel

@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 DATS = "/root/reference/OpenMP_and_MPI/gauss_openmp/matrices_dense"
 
 out = {}
-for name in ("matrix_10", "jpwh_991", "orsreg_1"):
+for name in ("matrix_10", "jpwh_991", "orsreg_1", "sherman5", "saylr4", "sherman3", "memplus"):
     path = os.path.join(DATS, name + ".dat")
     with open(path) as f:
         n = int(f.readline().split()[0])
@@ -32,8 +32,10 @@ for name in ("matrix_10", "jpwh_991", "orsreg_1"):
     out[f"{name}_rows"] = np.array(rows, np.int32)
     out[f"{name}_cols"] = np.array(cols, np.int32)
     out[f"{name}_vals"] = np.array(vals, np.float64)
-    res = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "gauss_external_input"), path, "4"],
+    res = subprocess.run([os.path.join(ROOT, "oracle", "_ref", "gauss_external_input"), path, str(os.cpu_count() or 4)],
                          capture_output=True, text=True).stdout
+    out[f"{name}_ref_seconds"] = np.array(float(re.search(r"Time:\s+(\S+) seconds", res).group(1)))
+    print(name, n, res.strip().splitlines()[-2:], flush=True)
     out[f"{name}_ref_error"] = np.array(float(re.search(r"Error: (\S+)", res).group(1)))
     # the file itself, verbatim, for the small ones: the parser tests read it back through the harness/ABI
     if name in ("matrix_10",):
