@@ -210,8 +210,9 @@ struct gauss_cuda_ctx {
     unsigned* push_counters = nullptr;          // device: completion counters of the two pushing kernels
     unsigned solve_seq = 0;                     // factorisations run by this context (every rank counts alike): flag values are seq * nblk + K + 1
     bool memops = false;                        // cuStreamWaitValue32 available (else a spinning one-warp kernel waits)
-    int cp_near = 3;                            // outer blocks after the crit block whose U12^T travels (and is applied) ahead of the rest (GAUSS_CUDA_CP_NEAR)
+    int cp_near = 8;                            // outer blocks after the crit block whose U12^T travels (and is applied) ahead of the rest (GAUSS_CUDA_CP_NEAR)
     cudaEvent_t ev_near[2] = {nullptr, nullptr}, ev_nearlocal[2] = {nullptr, nullptr}, ev_rownear[2] = {nullptr, nullptr};
+    cudaEvent_t ev_nearsplit[2] = {nullptr, nullptr};
     bool pdl_single = false;                    // GAUSS_CUDA_PDL_SINGLE=1: the same along the single-GPU panel chain
     bool pdl = true;                            // GAUSS_CUDA_PDL=0: the chain's kernels are launched without programmatic dependent launch
     double host_issue_ms = 0.0;                 // host time spent issuing the last factorisation (trace)
@@ -377,7 +378,7 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         const char* pd = getenv("GAUSS_CUDA_PDL");
         if (pd) c->pdl = atoi(pd) != 0;
         const char* nr = getenv("GAUSS_CUDA_CP_NEAR");
-        if (nr) c->cp_near = std::max(1, std::min(64, atoi(nr)));
+        if (nr) c->cp_near = std::max(2, std::min(64, atoi(nr)));     // >= 2: see the column bookkeeping in factor_cp
         const char* nbk = getenv("GAUSS_CUDA_CP_NOBULK");
         c->cp_nobulk = nbk && atoi(nbk) != 0;
     }
@@ -464,7 +465,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
                               &c->ev_ut[0], &c->ev_ut[1], &c->ev_utlocal[0], &c->ev_utlocal[1], &c->ev_utfree[0], &c->ev_utfree[1],
                               &c->ev_la[0], &c->ev_la[1], &c->ev_colstrip[0], &c->ev_colstrip[1], &c->ev_rowrest[0], &c->ev_rowrest[1],
                               &c->ev_inv[0], &c->ev_inv[1], &c->ev_p4a, &c->ev_wjoin,
-                              &c->ev_near[0], &c->ev_near[1], &c->ev_nearlocal[0], &c->ev_nearlocal[1], &c->ev_rownear[0], &c->ev_rownear[1]};
+                              &c->ev_near[0], &c->ev_near[1], &c->ev_nearlocal[0], &c->ev_nearlocal[1], &c->ev_rownear[0], &c->ev_rownear[1],
+                              &c->ev_nearsplit[0], &c->ev_nearsplit[1]};
         for (cudaEvent_t* ev : evs) if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
     }
     if (world > 1 || c->cp) {
@@ -485,8 +487,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         c->tr_ev.assign(8 * (size_t)c->nblk, nullptr);
         for (size_t i = 0; i < c->tr_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->tr_ev[i]);
     }
-    c->upd_ev.assign(6 * (size_t)c->nblk, nullptr);            // look-ahead splits the update in up to three launches
-    c->upd_flops.assign(3 * (size_t)c->nblk, 0.0);
+    c->upd_ev.assign(10 * (size_t)c->nblk, nullptr);           // the schedules split the update of a step in up to five launches
+    c->upd_flops.assign(5 * (size_t)c->nblk, 0.0);
     for (size_t i = 0; i < c->upd_ev.size() && e == cudaSuccess; ++i) e = cudaEventCreate(&c->upd_ev[i]);
     if (e != cudaSuccess) { int rc = cuda_fail(e, "context allocation", __LINE__); gauss_cuda_free(c); return rc; }
 
@@ -619,7 +621,8 @@ extern "C" void gauss_cuda_free(gauss_cuda_ctx* c)
                              c->ev_ut[0], c->ev_ut[1], c->ev_utlocal[0], c->ev_utlocal[1], c->ev_utfree[0], c->ev_utfree[1],
                              c->ev_la[0], c->ev_la[1], c->ev_colstrip[0], c->ev_colstrip[1], c->ev_rowrest[0], c->ev_rowrest[1],
                              c->ev_inv[0], c->ev_inv[1], c->ev_p4a, c->ev_wjoin,
-                             c->ev_near[0], c->ev_near[1], c->ev_nearlocal[0], c->ev_nearlocal[1], c->ev_rownear[0], c->ev_rownear[1]};
+                             c->ev_near[0], c->ev_near[1], c->ev_nearlocal[0], c->ev_nearlocal[1], c->ev_rownear[0], c->ev_rownear[1],
+                             c->ev_nearsplit[0], c->ev_nearsplit[1]};
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
     }
     if (!c->in_group) for (float* pb : c->peer_box) if (pb) cudaIpcCloseMemHandle(pb);
@@ -1336,6 +1339,7 @@ static int factor_cp(gauss_cuda_ctx* c)
         CK(cudaStreamWaitEvent(sp, c->ev_wjoin, 0));              // a12t is single-buffered too (previous row panel on the wide stream)
         if (have_rowrest) {                                        // the crit columns only need the near part of the previous step
             CK(cudaStreamWaitEvent(sp, c->ev_rownear[b ^ 1], 0));
+            CK(cudaStreamWaitEvent(sw, c->ev_rownear[b ^ 1], 0));
             CK(cudaStreamWaitEvent(sw, c->ev_rowrest[b ^ 1], 0));
         }
         if (ccrit > 0) {
@@ -1467,12 +1471,14 @@ static int factor_cp(gauss_cuda_ctx* c)
             return gemm_tc(c, ss, c->la_hi[b] + (size_t)ra * NB, c->la_lo[b] + (size_t)ra * NB, NB, c_uc_hi, c_uc_lo, NB,
                            c->W + (size_t)ra * ld + cnext, ld, rb - ra, rows_next, kb, -1, 1);
         };
-        // block column K+1 has received panel K-1's contribution through the bulk update of step K-1: that must be complete
-        // before this step's contribution is added and the column is read (next A21 split, next diagonal region)
+        // Column bookkeeping.  Panel j reaches block column J through: the column strip (J = j+1, this stream), the NEAR
+        // update (j+2 <= J <= j+1+near, this stream, below) or the FAR update (J beyond, main stream).  Block column K+1 is
+        // read here (next A21 split, next diagonal region) and block column K+2 by the next row panel's crit columns: with
+        // near >= 2 the far updates they depend on are those of steps <= K-2, which ev_free[b] above already covers; all
+        // near updates and column strips precede this point in stream order.
         if (own_next) {                                            // the rows of block K+1 first: they complete the next diagonal region
             PdlScope pdl_on(c->pdl);
             if ((rc = l21_rows(l0, l1))) return rc;
-            CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
             if (from_box && (rc = wait_flag(ss, 32, seq_of(K)))) return rc;
             if ((rc = colstrip_rows(l0, l1))) return rc;
             CK(cudaEventRecord(c->ev_colstrip[b], ss));
@@ -1484,7 +1490,6 @@ static int factor_cp(gauss_cuda_ctx* c)
             if ((rc = l21_rows(l0, c->rows_local))) return rc;
             CK(cudaEventRecord(c->ev_la[b], ss));
             mark(1, ss);
-            CK(cudaStreamWaitEvent(ss, c->ev_free[b ^ 1], 0));
             if ((rc = colstrip_rows(l0, c->rows_local))) return rc;
             CK(cudaEventRecord(c->ev_colstrip[b], ss));
         }
@@ -1493,6 +1498,22 @@ static int factor_cp(gauss_cuda_ctx* c)
         if (c->rows_local - l1 > 0 && K + 2 < nblk)
             launch_split_rowmajor(c->W + (size_t)l1 * ld + cnext, ld, c->as_[0] + (size_t)l1 * NB, c->as_[1] + (size_t)l1 * NB, NB,
                                   c->rows_local - l1, rows_next, ss);
+        // near columns of U12^T(K): B operand, then the near update of every local row below block K (the rows of block K+1
+        // first on its owner: its row panel's crit columns wait for them)
+        const int cn = std::max(cnext, near_end(K)), cfirst = cnext + rows_next;    // first far column, first column right of block K+1
+        const PanelRef pr{nullptr, 0, nullptr, 0, c->ub_hi[b], c->ub_lo[b]};
+        {
+            const StepBufs sbs{ss, c->la_hi[b], c->la_lo[b]};
+            CK(cudaStreamWaitEvent(ss, c->ev_near[b], 0));
+            launch_split_rowmajor(c->ut[b] + (size_t)cnext * NB, NB, c->ub_hi[b] + (size_t)cnext * NB, c->ub_lo[b] + (size_t)cnext * NB, NB,
+                                  cn - cnext, kb, ss);
+            CK(cudaEventRecord(c->ev_nearsplit[b], ss));
+            if (own_next) {
+                if (cn > cfirst && (rc = trailing_update(c, K, pr, sbs, l0, l1, cfirst, cn - cfirst))) return rc;
+                CK(cudaEventRecord(c->ev_rownear[b], ss));
+            }
+            if (cn > cfirst && !c->cp_nobulk && (rc = trailing_update(c, K, pr, sbs, l1, c->rows_local, cfirst, cn - cfirst, 0, c->cp_reserve))) return rc;
+        }
 
         // 2. panel stream (owner of K+1): its diagonal region is final after the column strip
         if (own_next) {
@@ -1501,23 +1522,15 @@ static int factor_cp(gauss_cuda_ctx* c)
             mark(3, sp);
         }
 
-        // 3. main stream: U12^T of step K arrives -> B operand; the rest of block K+1's rows
-        const int cn = std::max(cnext, near_end(K)), cfirst = cnext + rows_next;    // first far column, first column right of block K+1
-        const PanelRef pr{nullptr, 0, nullptr, 0, c->ub_hi[b], c->ub_lo[b]};
+        // 3. main stream: the far columns of U12^T(K) arrive -> B operand; the far part of block K+1's rows
         const StepBufs sbm{s, c->la_hi[b], c->la_lo[b]};
-        CK(cudaStreamWaitEvent(s, c->ev_near[b], 0));
-        launch_split_rowmajor(c->ut[b] + (size_t)cnext * NB, NB, c->ub_hi[b] + (size_t)cnext * NB, c->ub_lo[b] + (size_t)cnext * NB, NB,
-                              cn - cnext, kb, s);
-        CK(cudaStreamWaitEvent(s, c->ev_la[b], 0));
-        if (own_next) {                                            // near columns of block K+1's rows: all its crit columns depend on
-            if (cn > cfirst && (rc = trailing_update(c, K, pr, sbm, l0, l1, cfirst, cn - cfirst))) return rc;
-            CK(cudaEventRecord(c->ev_rownear[b], s));
-        }
         CK(cudaStreamWaitEvent(s, c->ev_ut[b], 0));
         mark(6, s);
         if (ld > cn)
             launch_split_rowmajor(c->ut[b] + (size_t)cn * NB, NB, c->ub_hi[b] + (size_t)cn * NB, c->ub_lo[b] + (size_t)cn * NB, NB, ld - cn, kb, s);
+        CK(cudaStreamWaitEvent(s, c->ev_nearsplit[b], 0));          // ut[b] is free once both parts have been split
         CK(cudaEventRecord(c->ev_utfree[b], s));
+        CK(cudaStreamWaitEvent(s, c->ev_la[b], 0));
         if (own_next) {
             if (ld > std::max(cn, cfirst) && (rc = trailing_update(c, K, pr, sbm, l0, l1, std::max(cn, cfirst), -1))) return rc;
             CK(cudaEventRecord(c->ev_rowrest[b], s));
@@ -1528,8 +1541,8 @@ static int factor_cp(gauss_cuda_ctx* c)
         // 5. communication of step K+1
         if ((rc = comm(K + 1))) return rc;
         // 6. bulk of the trailing update (CTAs give up their SM every few tiles: the other streams have priority)
-        if (!c->cp_nobulk &&
-            (rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, cnext + rows_next, -1,
+        if (!c->cp_nobulk && ld > std::max(cn, cfirst) &&
+            (rc = trailing_update(c, K, pr, sbm, l1, c->rows_local, std::max(cn, cfirst), -1,
                                   c->cp_reserve > 0 ? 0 : c->overlap_max_tiles, c->cp_reserve))) return rc;
         CK(cudaEventRecord(c->ev_free[b], s));
         mark(5, s);
