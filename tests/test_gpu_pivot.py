@@ -64,12 +64,18 @@ def test_without_pivoting_the_same_system_fails_or_is_wrong(mode):
     assert ol.max_rel_error(X, Xpre) <= TOL
 
 
+ALL_DAT = ["matrix_10", "jpwh_991", "orsreg_1", "sherman5", "saylr4", "sherman3", "memplus"]     # every file the reference ships
+
+
 @pytest.mark.parametrize("mode", MODES)
-@pytest.mark.parametrize("name", ["matrix_10", "jpwh_991", "orsreg_1"])
+@pytest.mark.parametrize("name", ALL_DAT)
 def test_reference_matrices(external, name, mode):
     A = ol.coo_to_dense(external, name)
     R, Xpre = ol.init_rhs(A)
-    Xo = ol.gauss_pivot(A, R, nthreads=4)
+    n = A.shape[0]
+    if name == "memplus" and mode == pkg.MODE_FFMA:
+        pytest.skip("order 17758 once is enough (3xTF32 mode)")
+    Xo = ol.gauss_pivot(A, R, nthreads=8) if n <= 2500 else None          # the CPU oracle only where it takes seconds
     X = pkg.gauss(A, R, mode=mode, pivoting=True)
     # the reference's own metric (:246-253) against the preset solution; FP32 instead of double, so the
     # bound is the north_star's 1e-3 rather than the reference's 1e-15 .. 1e-10
@@ -80,12 +86,15 @@ def test_reference_matrices(external, name, mode):
     assert ol.scaled_residual(A, R, X) <= 10.0
     # ... the forward error only where FP32 can deliver it: the reference's double-precision error times
     # eps32/eps64 = 2^29 predicts what the same elimination gives in single (orsreg_1: 2.2e-10 -> ~0.1)
+    # (the 3xTF32 mode carries ~2^-21 per product -- the dropped lo*lo term and the truncating splits of the panel
+    # solves -- against 2^-24 for the FFMA mode, hence the wider factor)
     predicted = ref_err * 2.0 ** 29
     if predicted <= TOL / 10:
         assert err <= TOL
-        assert ol.max_rel_error(X, Xo) <= TOL
+        if Xo is not None:
+            assert ol.max_rel_error(X, Xo) <= TOL
     else:
-        assert err <= 10 * predicted
+        assert err <= (100 if mode == pkg.MODE_3XTF32 else 10) * predicted
     if name == "matrix_10":
         assert ol.max_rel_error(X, Xpre) == 0.0            # the reference prints "Error: 0.000000e+00" for it
 
@@ -107,9 +116,10 @@ def test_pivoting_with_refinement_matches_oracle_in_double(n, seed, mode):
     assert ol.max_rel_error(X32, Xpre) <= TOL
 
 
-@pytest.mark.parametrize("name", ["matrix_10", "jpwh_991", "orsreg_1"])
+@pytest.mark.parametrize("name", ALL_DAT)
 def test_reference_matrices_in_double(external, name):
-    # the reference prints Error: 0 / 4.8e-15 / 2.2e-10 for these files in double; FP32 alone gives up to 5e-2 on orsreg_1
+    # the reference prints Error: 0 / 4.8e-15 / 2.2e-10 / 3.1e-13 / 4.2e-9 / 4.5e-13 / 9.9e-9 for these files in double;
+    # FP32 alone gives up to 5e-2 on orsreg_1
     A = ol.coo_to_dense(external, name)
     R, Xpre = ol.init_rhs(A)
     n = A.shape[0]
@@ -118,8 +128,10 @@ def test_reference_matrices_in_double(external, name):
         X, info = g.gauss_refined(A, R, max_iters=40)
     err = ol.max_rel_error(X, Xpre)
     ref_err = float(external[f"{name}_ref_error"])
-    print(name, "Error (GPU, refined):", err, " reference (double):", ref_err, "sweeps:", info.iterations,
-          "converged:", info.converged, "last correction:", info.last_correction)
+    print(name, "n", n, "Error (GPU, refined):", err, " reference (double):", ref_err, "sweeps:", info.iterations,
+          "converged:", info.converged, "last correction:", info.last_correction,
+          "| GPU seconds: FP32 elimination incl. upload %.4f + refinement %.4f" % (info.factor_s, info.refine_s),
+          "| reference program (8 host cores of the build container): %.2f s" % float(external[f"{name}_ref_seconds"]))
     assert info.converged in (1, 2)                        # 2: stagnated at what double residuals resolve (orsreg_1)
     assert err <= max(100 * ref_err, 1e-11)
 

@@ -109,13 +109,14 @@ def external():
     return np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "external_vectors.npz"))
 
 
-@pytest.mark.parametrize("name", ["matrix_10", "jpwh_991", "orsreg_1"])
+# (memplus, order 17758, is pinned through the GPU tests only: the CPU elimination takes the reference 15 minutes)
+@pytest.mark.parametrize("name", ["matrix_10", "jpwh_991", "orsreg_1", "sherman5", "saylr4", "sherman3"])
 def test_pivoting_oracle_reproduces_reference_error(external, name):
     # the value the unmodified reference binary prints as "Error:" for this file; jpwh_991's 4.814101e-15
     # is also the number shown in the reference's report (Pthreads/report.pdf p.3)
     A = ol.coo_to_dense(external, name)
     R, Xpre = ol.init_rhs(A)
-    X = ol.gauss_pivot(A, R, nthreads=4)
+    X = ol.gauss_pivot(A, R, nthreads=8)
     err = ol.max_rel_error(X, Xpre)
     want = float(external[f"{name}_ref_error"])
     assert abs(err - want) <= 1e-6 * max(want, 1e-300) + 1e-20, (err, want)
