@@ -150,7 +150,7 @@ struct gauss_cuda_ctx {
     bool wide_split = true;                     // GAUSS_CUDA_WIDE_SPLIT=0 keeps P1 on one stream
     cudaEvent_t ev_inner[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr}, ev_side = nullptr;
     cudaEvent_t ev_fork[2] = {nullptr, nullptr}, ev_join[2] = {nullptr, nullptr};
-    bool overlap = false;
+    const bool overlap = false;                 // (a single-GPU outer look-ahead was measured in round 1 and dropped: no gain)
     int overlap_max_tiles = 3;
     bool dist_pair = true;                      // GAUSS_CUDA_DIST_PAIR=0: multi-GPU updates stay on the single-CTA kernel
     float* ub_hi[2] = {nullptr, nullptr};       // [ld x NB]          split U operand, transposed;
@@ -213,7 +213,6 @@ struct gauss_cuda_ctx {
     int cp_near = 8;                            // outer blocks after the crit block whose U12^T travels (and is applied) ahead of the rest (GAUSS_CUDA_CP_NEAR)
     cudaEvent_t ev_near[2] = {nullptr, nullptr}, ev_nearlocal[2] = {nullptr, nullptr}, ev_rownear[2] = {nullptr, nullptr};
     cudaEvent_t ev_nearsplit[2] = {nullptr, nullptr};
-    bool pdl_single = false;                    // GAUSS_CUDA_PDL_SINGLE=1: the same along the single-GPU panel chain
     bool pdl = true;                            // GAUSS_CUDA_PDL=0: the chain's kernels are launched without programmatic dependent launch
     double host_issue_ms = 0.0;                 // host time spent issuing the last factorisation (trace)
     bool cp_nobulk = false;                     // GAUSS_CUDA_CP_NOBULK=1: timing diagnostic only (WRONG results): the bulk update is skipped
@@ -353,12 +352,8 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
     gauss_cuda_ctx* c = new gauss_cuda_ctx();
     c->n = n; c->rank = rank; c->world = world; c->device = device; c->mode = mode; c->in_group = in_group;
     { const char* g = getenv("GAUSS_CUDA_GRAPH"); if (g && atoi(g) == 0) c->use_graph = false; }
-    { const char* g = getenv("GAUSS_CUDA_PDL_SINGLE"); c->pdl_single = g ? atoi(g) != 0 : false; }
-    {   // single-GPU look-ahead (GAUSS_CUDA_OVERLAP=1): measured on B200 it is a wash -- the urow/lcol kernels are
-        // throughput-bound, so running them beside the bulk update only moves SM time around (N=32768: 132.0 ms
-        // with, 128.7 ms without) -- and it is therefore off unless asked for
-        const char* o = getenv("GAUSS_CUDA_OVERLAP");
-        c->overlap = world == 1 && o && atoi(o) != 0;
+    { const char* pd = getenv("GAUSS_CUDA_PDL"); if (pd) c->pdl = atoi(pd) != 0; }
+    {   // tiles a CTA of the bulk update takes before it gives its SM up (round-1 multi-GPU look-ahead)
         const char* mt = getenv("GAUSS_CUDA_OVERLAP_TILES");
         if (mt && atoi(mt) > 0) c->overlap_max_tiles = atoi(mt);
     }
@@ -375,8 +370,6 @@ static int ctx_create(gauss_cuda_ctx** out, int n, int rank, int world, int devi
         const char* r = getenv("GAUSS_CUDA_CP_RESERVE");
         if (r) c->cp_reserve = std::max(0, std::min(64, atoi(r)));
         if (!r) c->cp_reserve = world >= 4 ? 32 : 16;
-        const char* pd = getenv("GAUSS_CUDA_PDL");
-        if (pd) c->pdl = atoi(pd) != 0;
         const char* nr = getenv("GAUSS_CUDA_CP_NEAR");
         if (nr) c->cp_near = std::max(2, std::min(64, atoi(nr)));     // >= 2: see the column bookkeeping in factor_cp
         const char* nbk = getenv("GAUSS_CUDA_CP_NOBULK");
@@ -886,7 +879,9 @@ static int trailing_update(gauss_cuda_ctx* c, int K, const PanelRef& pr, const S
 static int outer_step(gauss_cuda_ctx* c, int K, int row_hi, float* ubh, float* ubl)
 {
     cudaStream_t s = c->s_main, ss = c->s_side, sw = c->s_wide;
-    PdlScope pdl_on(c->pdl_single);                             // the panel chain's kernels release their successors early
+    // plain launches: the panel chain's kernels release their successors early (measured N=2048: 0.99 -> 0.95 ms); under
+    // graph capture the replay already has no launch gaps and the attribute bought nothing (0.90 ms either way)
+    PdlScope pdl_on(c->pdl && !c->capturing);
     const int ld = c->ld, NB = c->NB, np = c->np;
     const bool tc = c->mode == GAUSS_CUDA_MODE_3XTF32;
     float* lah = c->la_hi[0]; float* lal = c->la_lo[0];
@@ -1045,52 +1040,6 @@ static int factor_streamed(gauss_cuda_ctx* c, const float* A, const float* B)
     }
     CK(cudaGetLastError());
     c->factored = true;
-    return GAUSS_CUDA_OK;
-}
-
-// Single GPU with look-ahead on a second, higher-priority stream.  Step K first updates the strips the next
-// panel needs (the rows of block K+1, then the columns of block K+1 for the rows below), forks the whole panel
-// path of block K+1 (P1 + P2) onto the panel stream, and runs the bulk of the trailing update beside it; the
-// tile engine's CTAs give up their SM after a few tiles so the small, latency-bound panel kernels get in.
-// L21 and U12 splits are double buffered by the parity of K (the panel path writes the next step's while the
-// bulk update still reads this step's).
-static int factor_overlap(gauss_cuda_ctx* c)
-{
-    cudaStream_t s = c->s_main, sp = c->s_panel;
-    const int ld = c->ld, NB = c->NB;
-    int rc;
-    {   // block 0: nothing to overlap with
-        const StepBufs sb0{s, c->la_hi[0], c->la_lo[0]};
-        if ((rc = panel_factor(c, 0, c->ub_hi[0], c->ub_lo[0], sb0))) return rc;
-        const float* P0 = c->W;
-        PanelRef pr0{P0, ld, P0 + blk_rows(c, 0), ld, c->ub_hi[0], c->ub_lo[0]};
-        if ((rc = col_panel(c, 0, pr0, NB, sb0))) return rc;
-    }
-    for (int K = 0; K < c->nblk; ++K) {
-        const int b = K & 1, k0 = K * NB, kb = blk_rows(c, K);
-        const StepBufs sb{s, c->la_hi[b], c->la_lo[b]};
-        const float* P0 = c->W + (size_t)k0 * ld + k0;
-        PanelRef pr{P0, ld, P0 + kb, ld, c->ub_hi[b], c->ub_lo[b]};
-        const int l0 = k0 + kb;                                   // first row below the panel
-        if (K + 1 >= c->nblk) break;                              // the last block has no rows below it
-        const int rows_next = blk_rows(c, K + 1);
-        const int l1 = l0 + rows_next;                            // first row below block K+1
-        // strips the next panel depends on
-        if ((rc = trailing_update(c, K, pr, sb, l0, l1))) return rc;                          // rows of block K+1, all columns
-        if ((rc = trailing_update(c, K, pr, sb, l1, c->rows_local, l0, rows_next))) return rc; // rows below, columns of block K+1
-        CK(cudaEventRecord(c->ev_fork[b], s));
-        // panel path of block K+1 on the panel stream
-        CK(cudaStreamWaitEvent(sp, c->ev_fork[b], 0));
-        const StepBufs sbn{sp, c->la_hi[b ^ 1], c->la_lo[b ^ 1]};
-        if ((rc = panel_factor(c, K + 1, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1], sbn))) return rc;
-        const float* P1 = c->W + (size_t)l0 * ld + l0;
-        PanelRef prn{P1, ld, P1 + rows_next, ld, c->ub_hi[b ^ 1], c->ub_lo[b ^ 1]};
-        if ((rc = col_panel(c, K + 1, prn, l1, sbn))) return rc;
-        CK(cudaEventRecord(c->ev_join[b], sp));
-        // the bulk of the update, beside it
-        if ((rc = trailing_update(c, K, pr, sb, l1, c->rows_local, l1, -1, c->overlap_max_tiles))) return rc;
-        CK(cudaStreamWaitEvent(s, c->ev_join[b], 0));
-    }
     return GAUSS_CUDA_OK;
 }
 
@@ -1592,7 +1541,7 @@ static int factor(gauss_cuda_ctx* c)
     int rc = c->pivot ? factor_pivot(c)
            : c->cp ? factor_cp(c)
            : c->world > 1 ? factor_lookahead(c)
-           : (c->overlap && c->nblk >= 3) ? factor_overlap(c) : factor_single(c);
+           : factor_single(c);
     c->host_issue_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - host_t0).count();
     if (rc) return rc;
     CK(cudaGetLastError());

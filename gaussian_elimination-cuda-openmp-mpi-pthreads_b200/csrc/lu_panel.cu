@@ -56,13 +56,6 @@ __device__ __forceinline__ bool bad_pivot(float p, float r)
     return !(fabsf(p) >= 1.17549435e-38f) || !(fabsf(r) >= 1.17549435e-38f) || isinf(p) || isinf(r);
 }
 
-struct DiagSmem {
-    float rowbuf[2][kNb];
-    float colbuf[2][kNb];
-    float rinv[kNb];
-    int first_bad;
-};
-
 struct DiagSmem2 {
     float rowbuf[2][2][kNb];
     float colbuf[2][2][kNb];
@@ -70,49 +63,10 @@ struct DiagSmem2 {
     int first_bad;
 };
 
-template <int PH>
-__device__ __forceinline__ void diag_phase(float (&a)[8][8], DiagSmem& sm, const int tx, const int ty)
-{
-#pragma unroll 1
-    for (int kk = 0; kk < 16; ++kk) {
-        const int k = PH * 16 + kk;
-        float* rb = sm.rowbuf[k & 1];
-        float* cb = sm.colbuf[k & 1];
-        if (ty == kk) {                                    // holders of row k: raw values, pivot included
-#pragma unroll
-            for (int q = PH; q < 8; ++q) rb[tx + 16 * q] = a[PH][q];
-        }
-        if (tx == kk) {                                    // holders of column k: raw multipliers a_ik
-#pragma unroll
-            for (int p = PH; p < 8; ++p) cb[ty + 16 * p] = a[p][PH];
-        }
-        __syncthreads();
-        const float piv = rb[k];
-        const float r = fast_rcp(piv);
-        if (tx == kk && ty == kk) {
-            sm.rinv[k] = r;
-            if (bad_pivot(piv, r)) atomicMin(&sm.first_bad, k);
-        }
-        // only the first row/column group of the phase can still contain indices <= k
-        float rv[8], lv[8];
-        rv[PH] = (tx > kk) ? rb[tx + 16 * PH] : 0.f;
-        lv[PH] = (ty > kk) ? cb[ty + 16 * PH] * r : 0.f;
-#pragma unroll
-        for (int q = PH + 1; q < 8; ++q) rv[q] = rb[tx + 16 * q];
-#pragma unroll
-        for (int p = PH + 1; p < 8; ++p) lv[p] = cb[ty + 16 * p] * r;
-#pragma unroll
-        for (int p = PH; p < 8; ++p)
-#pragma unroll
-            for (int q = PH; q < 8; ++q) a[p][q] = fmaf(-lv[p], rv[q], a[p][q]);     // computeGauss :132-134
-    }
-}
-
 // Two pivots per barrier.  Rows k, k+1 and columns k, k+1 are published raw; every thread then redoes the tiny
 // part of step k that step k+1 depends on (the 2x2 pivot block, its own entries of row k+1 and column k+1) and
 // applies both rank-1 updates back to back.  Each element sees exactly the operations of two single steps in the
-// same order, so the result is bit-identical to diag_phase; the barrier / publish / reload latency is paid once
-// per two pivots.
+// same order; the barrier / publish / reload latency is paid once per two pivots.
 template <int PH>
 __device__ __forceinline__ void diag_phase2(float (&a)[8][8], DiagSmem2& sm, const int tx, const int ty)
 {
@@ -176,44 +130,8 @@ __device__ __forceinline__ void diag_phase2(float (&a)[8][8], DiagSmem2& sm, con
     }
 }
 
-__global__ void __launch_bounds__(256, 1)
-diag_factor_kernel(float* __restrict__ blk, int ld, int grow0, int* __restrict__ status)
-{
-    __shared__ DiagSmem sm;
-    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    if (tid == 0) sm.first_bad = kNb;
-    float a[8][8];
-#pragma unroll
-    for (int p = 0; p < 8; ++p)
-#pragma unroll
-        for (int q = 0; q < 8; ++q) a[p][q] = blk[(size_t)(ty + 16 * p) * ld + tx + 16 * q];
-    diag_phase<0>(a, sm, tx, ty);
-    diag_phase<1>(a, sm, tx, ty);
-    diag_phase<2>(a, sm, tx, ty);
-    diag_phase<3>(a, sm, tx, ty);
-    diag_phase<4>(a, sm, tx, ty);
-    diag_phase<5>(a, sm, tx, ty);
-    diag_phase<6>(a, sm, tx, ty);
-    diag_phase<7>(a, sm, tx, ty);
-    __syncthreads();
-    // U to unit-diagonal form: row i (above the diagonal) times 1/pivot_i; L keeps the pivots
-#pragma unroll
-    for (int p = 0; p < 8; ++p) {
-        const int i = ty + 16 * p;
-        const float ri = sm.rinv[i];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int j = tx + 16 * q;
-            const float v = (j > i) ? a[p][q] * ri : a[p][q];
-            blk[(size_t)i * ld + j] = v;
-        }
-    }
-    // earliest bad pivot of this block; the first block to report wins (blocks run in pivot order)
-    if (tid == 0 && sm.first_bad < kNb) atomicCAS(status, 0, grow0 + sm.first_bad + 1);
-}
-
-// Default kernel: the same layout and the same arithmetic, two pivots per barrier.  Measured on B200: 23.9 us
-// against 27.3 us for one pivot per barrier, bit-identical output.  (Four pivots per barrier: 24.1 us, eight:
+// The kernel: two pivots per barrier.  Measured on B200: 23.9 us against 27.3 us for one pivot per barrier (a variant kept
+// through round 1 for A/B timing, bit-identical output).  (Four pivots per barrier: 24.1 us, eight:
 // 52 us -- the redundant work grows faster than the barrier count shrinks.  A variant blocked 32 wide with the
 // 32 sequential pivots inside one warp, rows exchanged by shuffle, took 52 us: a lone warp issues its
 // dependent shuffle/FMA stream at ~3 cycles per instruction.)
@@ -253,13 +171,9 @@ diag_factor_pair_kernel(float* __restrict__ blk, int ld, int grow0, int* __restr
     if (tid == 0 && sm.first_bad < kNb) atomicCAS(status, 0, grow0 + sm.first_bad + 1);
 }
 
-static int g_diag_variant = -1;          // GAUSS_CUDA_DIAG=0: one pivot per barrier (kept for A/B timing)
-
 void launch_diag_factor(float* blk, int ld, int global_row0, int* status, cudaStream_t s)
 {
-    if (g_diag_variant < 0) { const char* e = getenv("GAUSS_CUDA_DIAG"); g_diag_variant = e ? atoi(e) : 2; }
-    if (g_diag_variant == 0) diag_factor_kernel<<<1, 256, 0, s>>>(blk, ld, global_row0, status);
-    else launch_k(diag_factor_pair_kernel, dim3(1), dim3(256), 0, s, blk, ld, global_row0, status);
+    launch_k(diag_factor_pair_kernel, dim3(1), dim3(256), 0, s, blk, ld, global_row0, status);
     ++g_launch_count;
 }
 

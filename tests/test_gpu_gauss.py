@@ -70,18 +70,40 @@ def test_fixture_known_answer_at_scale(mode):
 
 
 @pytest.mark.parametrize("mode", MODES)
-def test_opt_in_schedules_give_the_same_answer(mode, monkeypatch):
-    # GAUSS_CUDA_OVERLAP=1 (panel path on a priority stream beside the bulk update) and GAUSS_CUDA_GRAPH=0
-    # (plain launches instead of graph replay) are read when the context is created
+def test_plain_launches_give_the_same_answer_as_graph_replay(mode, monkeypatch):
+    # GAUSS_CUDA_GRAPH=0 (plain launches instead of graph replay) is read when the context is created
     n = 2100
     A, B, Xtrue = pkg.initialize_inputs(n, 12)
-    X0 = pkg.gauss(A, B, mode=mode, nb=512)
-    monkeypatch.setenv("GAUSS_CUDA_OVERLAP", "1")
-    X1 = pkg.gauss(A, B, mode=mode, nb=512)
+    with pkg.GaussCuda(n, mode=mode, nb=512) as g:
+        g.upload(A, B)
+        g.solve_resident()
+        assert g.stats.graph_replayed == 1
+        X0 = g.download()
     monkeypatch.setenv("GAUSS_CUDA_GRAPH", "0")
-    X2 = pkg.gauss(A, B, mode=mode, nb=512)
+    with pkg.GaussCuda(n, mode=mode, nb=512) as g:
+        g.upload(A, B)
+        g.solve_resident()
+        assert g.stats.graph_replayed == 0
+        X2 = g.download()
     assert ol.max_rel_error(X0, Xtrue) <= TOL
-    assert np.array_equal(X0, X1) and np.array_equal(X1, X2)     # same kernels, same tile shapes, same order of sums
+    assert np.array_equal(X0, X2)                                # same kernels, same tile shapes, same order of sums
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_critical_path_schedule_on_one_gpu(mode, monkeypatch):
+    # GAUSS_CUDA_SCHED=cp runs the multi-GPU schedule (diagonal region in the extended scratch, inverse-based panel GEMMs,
+    # near / far updates) with a single rank: same tolerance against the oracle, and the fixture's exact answer
+    monkeypatch.setenv("GAUSS_CUDA_SCHED", "cp")
+    for n, nb in ((300, 128), (1500, 512), (2100, 256)):
+        A, B, Xtrue = pkg.initialize_inputs(n, 3)
+        Xref, Bref, _ = ol.gauss(A, B, nthreads=8)
+        X, Bafter = pkg.gauss(A, B, mode=mode, nb=nb, want_b_after=True)
+        assert ol.max_rel_error(X, Xref) <= TOL and ol.max_rel_error(Bafter, Bref) <= TOL
+        assert ol.scaled_residual(A, B, X) <= 10.0
+    A, B = pkg.initMatrix(2048)
+    X, Bafter = pkg.gauss(A, B, mode=mode, nb=256, want_b_after=True)
+    wx, wb = fixture_answer(2048)
+    assert np.array_equal(X, wx) and np.array_equal(Bafter, wb)
 
 
 @pytest.mark.parametrize("mode", MODES)
