@@ -112,6 +112,11 @@ def test_harness_cli_help_and_missing_gpu():
     if pkg.device_count() == 0:
         out = subprocess.run([exe, "-s", "64"], capture_output=True, text=True)
         assert out.returncode == 2 and "Matrix Size: 64" in out.stdout and "CUDA" in out.stderr
+        # -g G (several GPUs from this one process): a group needs G visible devices -- loud failure, no fallback
+        out = subprocess.run([exe, "-s", "64", "-g", "2"], capture_output=True, text=True)
+        assert out.returncode == 2 and "GPUs asked for" in out.stderr
+    out = subprocess.run([exe, "-s", "64", "-g", "0"], capture_output=True, text=True)
+    assert "GPU count should be a natural number" in out.stderr
 
 
 def test_external_harness_parses_its_arguments_without_gpu(tmp_path):
