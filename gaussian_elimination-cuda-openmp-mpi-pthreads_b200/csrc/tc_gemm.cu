@@ -19,6 +19,7 @@
 #include <cuda.h>
 #include <stdio.h>
 #include <algorithm>
+#include <atomic>
 
 namespace gb200 {
 
@@ -667,7 +668,7 @@ static int g_num_sms = 0;
 constexpr int kSchedSlots = 64;
 static __device__ int g_sched_slots[2 * kSchedSlots];
 static int* g_sched_addr[16] = {nullptr};
-static unsigned g_sched_next = 0;
+static std::atomic<unsigned> g_sched_next{0};   // (contexts of a single-process group launch from several host threads)
 // Callers that replay their launches from a CUDA graph own their scheduler slots (so two graphs running
 // on different streams can never share one); everyone else uses the library's ring.
 static thread_local int* t_sched_override = nullptr;
@@ -759,7 +760,7 @@ static int launch_variant(const float* Ahi, const float* Alo, int lda, const flo
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
-    int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
+    int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next.fetch_add(1, std::memory_order_relaxed) % kSchedSlots);
     launch_k(tc_gemm_kernel<BK, STAGES>, dim3(grid), dim3(kTcThreads), (size_t)Cfg::smem_bytes, s, ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0, sched, dyn, max_tiles);
     ++g_launch_count;
     return (int)cudaGetLastError();
@@ -793,7 +794,7 @@ static int launch_pair(const float* Ahi, const float* Alo, int lda, const float*
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 16 || !g_sched_addr[dev]) return (int)cudaErrorInvalidValue;
-    int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next++ % kSchedSlots);
+    int* sched = (t_sched_override ? t_sched_override : g_sched_addr[dev]) + 2 * (g_sched_next.fetch_add(1, std::memory_order_relaxed) % kSchedSlots);
     launch_k(tc_gemm_pair_kernel<BK, STAGES>, dim3(2 * pairs), dim3(kTcThreads), (size_t)Cfg::smem_bytes, s, ta, tal, tb, tbl, tc, m, n, k, sign < 0 ? 1 : 0, beta ? 1 : 0,
              sched, dyn, max_tiles);
     ++g_launch_count;
