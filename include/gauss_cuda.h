@@ -30,7 +30,8 @@
 extern "C" {
 #endif
 
-typedef struct gauss_cuda_ctx gauss_cuda_ctx;   /* opaque: device buffers, streams, NCCL communicator */
+typedef struct gauss_cuda_ctx gauss_cuda_ctx;   /* opaque: device buffers, streams, NCCL communicator, peer mappings;
+                                                 * for ngpus > 1 a handle on one such context per device */
 
 enum {
     GAUSS_CUDA_OK         = 0,
@@ -48,7 +49,8 @@ enum {
 
 typedef struct {
     double h2d_s, factor_s, backsub_s, d2h_s;   /* CUDA-event times of the last call, seconds */
-    double bcast_bytes;                         /* bytes this rank received over NCCL in the last call */
+    double bcast_bytes;                         /* bytes this rank received from the other ranks in the last call (NCCL
+                                                 * broadcasts of the panels plus the x_K written into its memory by peers) */
     int    zero_pivot_row;                      /* -1, or the global row of the first bad pivot */
     int    n, n_padded, nb_outer, nb_inner, mode, rank, world;
     long long kernel_launches;                  /* kernels this library launched in the last call */
@@ -84,7 +86,10 @@ int gauss_cuda_init(gauss_cuda_ctx **ctx, int n, int ngpus, int nb, int mode);
  * MPI_Bcast(&matrix[i][i+1], ...) (gauss_mpi/gauss_internal_input.c:137) becomes one NCCL
  * broadcast of the factored row panel per outer block.  `nccl_id` is 128 bytes obtained
  * from gauss_cuda_unique_id() on rank 0 and handed to every rank by the launcher
- * (torch.distributed, MPI, a file ...).  Collective: every rank must call it. */
+ * (torch.distributed, MPI, a file ...).  Collective: every rank must call it.  In 3xTF32 mode the ranks also map each
+ * other's receive buffers (CUDA IPC; needs peer access between the GPUs, as NVLink / NVSwitch give): what the next
+ * panel needs first and the solution blocks of back substitution are stored there by the producing kernels themselves;
+ * without peer access the same data travels by NCCL only. */
 int gauss_cuda_unique_id(void *nccl_id_128);
 int gauss_cuda_init_dist(gauss_cuda_ctx **ctx, int n, int rank, int world, int device,
                          const void *nccl_id_128, int nb, int mode);
