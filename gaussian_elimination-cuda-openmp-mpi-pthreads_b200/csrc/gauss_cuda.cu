@@ -14,8 +14,12 @@
 // which reproduces computeGauss (gauss_internal_input.c:118-138) up to rounding order; back
 // substitution (solveGauss :144-159) runs block-wise from the last outer block up.
 // Schedules: factor_single (one GPU, captured into a CUDA graph; P2 and the wide part of P1 on side streams),
-// factor_streamed (one GPU, host data: upload overlapped, up-looking across row chunks), factor_lookahead
-// (multi-GPU pipeline), factor_pivot (external-input variant), gauss_cuda_solve_refined (double-precision answers).
+// factor_streamed (one GPU, host data: upload overlapped, up-looking across row chunks), factor_cp (multi-GPU, 3xTF32:
+// the critical-path schedule -- diagonal region in an extended scratch that yields inv(L11) / inv(U11), panel solves as
+// single GEMMs, the next panel's needs pushed into the next owner's memory, near / far U12 broadcasts; lu_cp.cu),
+// factor_lookahead (multi-GPU, FFMA mode: the round-1 pipeline), factor_pivot (external-input variant),
+// gauss_cuda_solve_refined (double-precision answers).  Multi-GPU contexts are either one rank per process
+// (gauss_cuda_init_dist) or a group of rank contexts inside one process, driven by library threads (gauss_cuda_init).
 #include "gauss_cuda.h"
 #include "gauss_internal.cuh"
 
